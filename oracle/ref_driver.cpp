@@ -1,0 +1,180 @@
+// TEST INFRASTRUCTURE (oracle) -- not part of the product path.
+//
+// Oracle driver: our own main() around the UNMODIFIED reference code.  The
+// reference's render.cpp is included as a translation unit (path_tracing.h /
+// vol_path_tracing.h define non-inline functions and may live in one TU only,
+// SURVEY.md appendix A.10), so this file can call path_tracing(),
+// vol_path_tracing*() and render() directly.
+//
+//   ref_driver render <scene.xml> -o out.pfm [--spp N] [--mode A|B] [-t T]
+//                     [--tiles i/n] [--stats stats.json]
+//       mode A : the reference's own render() (render.cpp:155) -- one pcg32
+//                stream per 16x16 tile, init_pcg32(ty*ntx+tx) (render.cpp:82).
+//       mode B : same integrators, but one pcg32 stream per (pixel, sample):
+//                init_pcg32(s*w*h + y*w + x).  This is the stream layout of
+//                the GPU wavefront renderer; it lets the GPU be compared with
+//                the reference path by path without serialising a tile.
+//   ref_driver hits <scene.xml> -o hits.bin
+//       primary-ray closest hits through the reference's intersect() for the
+//       pixel-centre ray of every pixel (aux_render's ray, render.cpp:27):
+//       per pixel {float t,u,v; int geomID, primID} with t = distance.
+//   ref_driver rng <n>
+//       first n next_pcg32_real<double> draws of init_pcg32(7) (known-answer
+//       vector for pcg.h:32-67).
+#include "render.cpp"   // found via -I$(REF)/src : /root/reference/src/render.cpp
+
+#include "parse_scene.h"
+#include "timer.h"
+#include <chrono>
+#include <unistd.h>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <string>
+#include <thread>
+
+extern "C" void lj_shim_ray_counts(uint64_t *isect, uint64_t *occl);
+extern "C" void lj_shim_reset_ray_counts();
+
+typedef Spectrum (*SampleFn)(const Scene &, int, int, pcg32_state &);
+
+static SampleFn pick_integrator(const Scene &scene, bool &is_vol) {
+    is_vol = false;
+    if (scene.options.integrator == Integrator::Path) return path_tracing;
+    if (scene.options.integrator == Integrator::VolPath) {
+        is_vol = true;
+        switch (scene.options.vol_path_version) { // render.cpp:111-124
+            case 1: return vol_path_tracing_1;
+            case 2: return vol_path_tracing_2;
+            case 3: return vol_path_tracing_3;
+            case 4: return vol_path_tracing_4;
+            case 5: return vol_path_tracing_5;
+            default: return vol_path_tracing;
+        }
+    }
+    return nullptr;
+}
+
+// Mode B: per-(pixel,sample) streams.  Accumulation order and the NaN filter
+// follow render.cpp:88-95 / :135-146.
+static Image3 render_mode_b(const Scene &scene, int s_begin, int s_end) {
+    int w = scene.camera.width, h = scene.camera.height;
+    Image3 img(w, h);
+    bool is_vol; SampleFn f = pick_integrator(scene, is_vol);
+    if (!f) { fprintf(stderr, "mode B needs a path/volpath integrator\n"); exit(2); }
+    constexpr int tile_size = 16;
+    int ntx = (w + tile_size - 1) / tile_size, nty = (h + tile_size - 1) / tile_size;
+    parallel_for([&](const Vector2i &tile) {
+        int x0 = tile[0] * tile_size, x1 = min(x0 + tile_size, w);
+        int y0 = tile[1] * tile_size, y1 = min(y0 + tile_size, h);
+        for (int y = y0; y < y1; y++) for (int x = x0; x < x1; x++) {
+            Spectrum radiance = make_zero_spectrum();
+            for (int s = s_begin; s < s_end; s++) {
+                pcg32_state rng = init_pcg32((uint64_t)s * (uint64_t)(w * h) + (uint64_t)(y * w + x));
+                Spectrum L = f(scene, x, y, rng);
+                if (!is_vol || isfinite(L)) radiance += L;
+            }
+            img(x, y) = radiance / Real(s_end - s_begin);
+        }
+    }, Vector2i(ntx, nty));
+    return img;
+}
+
+static int cmd_render(int argc, char **argv) {
+    std::string scene_file, out = "out.pfm", mode = "A", stats_file;
+    int spp = -1, threads = std::thread::hardware_concurrency();
+    int s_begin = 0, s_end = -1, max_depth = -100;
+    for (int i = 2; i < argc; i++) {
+        std::string a = argv[i];
+        if (a == "-o") out = argv[++i];
+        else if (a == "--spp") spp = atoi(argv[++i]);
+        else if (a == "--mode") mode = argv[++i];
+        else if (a == "-t") threads = atoi(argv[++i]);
+        else if (a == "--stats") stats_file = argv[++i];
+        else if (a == "--sample-range") { s_begin = atoi(argv[++i]); s_end = atoi(argv[++i]); }
+        else if (a == "--max-depth") max_depth = atoi(argv[++i]);
+        else scene_file = a;
+    }
+    char cwd[4096]; if (!getcwd(cwd, sizeof cwd)) return 2;
+    auto abs_path = [&](const std::string &p) { return (p.size() && p[0] == '/') ? p : std::string(cwd) + "/" + p; };
+    out = abs_path(out); if (!stats_file.empty()) stats_file = abs_path(stats_file);
+
+    RTCDevice dev = rtcNewDevice(nullptr);
+    parallel_init(threads);
+    auto t0 = std::chrono::steady_clock::now();
+    Scene scene = parse_scene(scene_file, dev); // chdir()s into the scene folder (parse_scene.cpp:1143)
+    if (spp > 0) scene.options.samples_per_pixel = spp;
+    if (max_depth != -100) scene.options.max_depth = max_depth;
+    auto t1 = std::chrono::steady_clock::now();
+    lj_shim_reset_ray_counts();
+    Image3 img;
+    if (mode == "A") img = render(scene);
+    else {
+        if (s_end < 0) s_end = scene.options.samples_per_pixel;
+        img = render_mode_b(scene, s_begin, s_end);
+    }
+    auto t2 = std::chrono::steady_clock::now();
+    uint64_t ni, no; lj_shim_ray_counts(&ni, &no);
+    imwrite(out, img);
+    double parse_s = std::chrono::duration<double>(t1 - t0).count();
+    double render_s = std::chrono::duration<double>(t2 - t1).count();
+    int nspp = (mode == "A") ? scene.options.samples_per_pixel : (s_end - s_begin);
+    double samples = double(scene.camera.width) * scene.camera.height * nspp;
+    char buf[1024];
+    snprintf(buf, sizeof buf,
+             "{\"scene\": \"%s\", \"mode\": \"%s\", \"width\": %d, \"height\": %d, \"spp\": %d, \"threads\": %d, "
+             "\"parse_s\": %.6f, \"render_s\": %.6f, \"samples\": %.0f, \"intersect_rays\": %llu, \"occluded_rays\": %llu, "
+             "\"msamples_per_s\": %.6f, \"mrays_per_s\": %.6f}",
+             scene_file.c_str(), mode.c_str(), scene.camera.width, scene.camera.height, nspp, threads,
+             parse_s, render_s, samples, (unsigned long long)ni, (unsigned long long)no,
+             samples / render_s * 1e-6, double(ni + no) / render_s * 1e-6);
+    printf("%s\n", buf);
+    if (!stats_file.empty()) { std::ofstream f(stats_file); f << buf << "\n"; }
+    parallel_cleanup();
+    return 0;
+}
+
+static int cmd_hits(int argc, char **argv) {
+    std::string scene_file, out = "hits.bin";
+    for (int i = 2; i < argc; i++) { std::string a = argv[i]; if (a == "-o") out = argv[++i]; else scene_file = a; }
+    char cwd[4096]; if (!getcwd(cwd, sizeof cwd)) return 2;
+    if (out[0] != '/') out = std::string(cwd) + "/" + out;
+    RTCDevice dev = rtcNewDevice(nullptr);
+    parallel_init(1);
+    Scene scene = parse_scene(scene_file, dev);
+    int w = scene.camera.width, h = scene.camera.height;
+    struct Rec { float t, u, v; int geom, prim; };
+    std::vector<Rec> recs(w * h);
+    for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) {
+        Ray ray = sample_primary(scene.camera, Vector2((x + Real(0.5)) / w, (y + Real(0.5)) / h));
+        Rec r{0, 0, 0, -1, -1};
+        if (std::optional<PathVertex> v = intersect(scene, ray, init_ray_differential(w, h))) {
+            r.t = (float)distance(v->position, ray.org); r.u = (float)v->st[0]; r.v = (float)v->st[1];
+            r.geom = v->shape_id; r.prim = v->primitive_id;
+        }
+        recs[y * w + x] = r;
+    }
+    std::ofstream f(out, std::ios::binary);
+    f.write((const char *)&w, 4); f.write((const char *)&h, 4);
+    f.write((const char *)recs.data(), recs.size() * sizeof(Rec));
+    printf("wrote %d x %d hit records to %s\n", w, h, out.c_str());
+    parallel_cleanup();
+    return 0;
+}
+
+static int cmd_rng(int argc, char **argv) {
+    int n = argc > 2 ? atoi(argv[2]) : 8;
+    pcg32_state rng = init_pcg32(7);
+    for (int i = 0; i < n; i++) printf("%.17g\n", next_pcg32_real<double>(rng));
+    return 0;
+}
+
+int main(int argc, char **argv) {
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|hits|rng ...\n"); return 2; }
+    std::string cmd = argv[1];
+    if (cmd == "render") return cmd_render(argc, argv);
+    if (cmd == "hits") return cmd_hits(argc, argv);
+    if (cmd == "rng") return cmd_rng(argc, argv);
+    fprintf(stderr, "unknown command %s\n", cmd.c_str());
+    return 2;
+}
