@@ -1,0 +1,265 @@
+// C ABI of include/lajolla_gpu.h: context, scene upload + BVH build, render
+// dispatch, batch ray casting, scene blobs.
+#include "lj_internal.h"
+#include "lj_traverse8.cuh"
+
+#include <cstdarg>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+static thread_local char g_err[1024] = "";
+
+void lj_set_error(const char *fmt, ...) {
+    va_list ap; va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+extern "C" const char *lj_last_error(void) { return g_err; }
+
+extern "C" int lj_init(int device_id, lj_ctx **out) {
+    if (!out) { lj_set_error("lj_init: out is null"); return LJ_EINVAL; }
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n == 0) {
+        lj_set_error("lj_init: no CUDA device (%s); this library has no CPU path", e == cudaSuccess ? "device count 0" : cudaGetErrorString(e));
+        return LJ_ENODEVICE;
+    }
+    if (device_id < 0 || device_id >= n) { lj_set_error("lj_init: device %d out of range [0,%d)", device_id, n); return LJ_EINVAL; }
+    LJ_CUDA(cudaSetDevice(device_id));
+    lj_ctx *c = new lj_ctx();
+    c->device = device_id;
+    LJ_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device_id));
+    *out = c;
+    return LJ_OK;
+}
+extern "C" void lj_shutdown(lj_ctx *ctx) { delete ctx; }
+
+template <typename T>
+static int upload(lj_scene *s, const T *host, size_t count, const T **dev) {
+    *dev = nullptr;
+    size_t bytes = sizeof(T) * (count ? count : 1);
+    void *p = nullptr;
+    LJ_CUDA(cudaMalloc(&p, bytes));
+    s->allocs.push_back(p);
+    if (count) LJ_CUDA(cudaMemcpy(p, host, sizeof(T) * count, cudaMemcpyHostToDevice));
+    *dev = (const T *)p;
+    return LJ_OK;
+}
+
+static int validate_desc(const lj_scene_desc *d) {
+    if (d->camera.width <= 0 || d->camera.height <= 0) { lj_set_error("scene: bad resolution %dx%d", d->camera.width, d->camera.height); return LJ_EINVAL; }
+    for (uint64_t i = 0; i < d->num_shapes; i++) {
+        const lj_shape &s = d->shapes[i];
+        if (s.kind == LJ_SHAPE_MESH) {
+            if ((uint64_t)s.vertex_offset + s.num_vertices > d->num_positions || (uint64_t)s.triangle_offset + s.num_triangles > d->num_indices) {
+                lj_set_error("scene: shape %llu mesh ranges out of bounds", (unsigned long long)i); return LJ_EINVAL;
+            }
+            for (uint32_t t = 0; t < s.num_triangles * 3; t++) {
+                int idx = d->indices[3 * (size_t)s.triangle_offset + t];
+                if (idx < 0 || (uint32_t)idx >= s.num_vertices) { lj_set_error("scene: shape %llu has an out-of-range vertex index", (unsigned long long)i); return LJ_EINVAL; }
+            }
+        }
+        if (s.material_id >= (int)d->num_materials) { lj_set_error("scene: shape %llu material id out of range", (unsigned long long)i); return LJ_EINVAL; }
+    }
+    if ((d->options.integrator == LJ_INTEGRATOR_PATH || d->options.integrator == LJ_INTEGRATOR_VOLPATH) && d->num_lights == 0) {
+        lj_set_error("scene: no lights (the reference asserts in sample(TableDist1D), table_dist.cpp:29)"); return LJ_EINVAL;
+    }
+    return LJ_OK;
+}
+
+extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene **out) {
+    if (!ctx || !desc || !out) { lj_set_error("lj_scene_create: null argument"); return LJ_EINVAL; }
+    int rc = validate_desc(desc);
+    if (rc) return rc;
+    LJ_CUDA(cudaSetDevice(ctx->device));
+    lj_scene *s = new lj_scene();
+    s->ctx = ctx; s->wf_pool = nullptr; s->wf_pool_bytes = 0; s->wf_capacity = 0;
+    memset(&s->build_stats, 0, sizeof s->build_stats);
+    memset(&s->bvh, 0, sizeof s->bvh);
+    DScene &d = s->d;
+    memset(&d, 0, sizeof d);
+    cudaEvent_t e0, e1, e2;
+    cudaEventCreate(&e0); cudaEventCreate(&e1); cudaEventCreate(&e2);
+    cudaEventRecord(e0);
+    d.camera = desc->camera; d.options = desc->options;
+    d.bounds_radius = desc->bounds_radius;
+    double e = desc->bounds_radius * 1e-5;            // scene.h:99-105
+    d.eps = e < 0.01 ? e : 0.01;
+    d.envmap_light_id = desc->envmap_light_id;
+    d.num_lights = (int)desc->num_lights; d.num_shapes = (int)desc->num_shapes; d.num_materials = (int)desc->num_materials;
+#define UP(field, cnt) if ((rc = upload(s, desc->field, (size_t)(cnt), &d.field)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+    UP(shapes, desc->num_shapes) UP(lights, desc->num_lights) UP(materials, desc->num_materials) UP(media, desc->num_media)
+    UP(textures, desc->num_textures) UP(images1, desc->num_images1) UP(images3, desc->num_images3)
+    UP(positions, desc->num_positions * 3) UP(normals, desc->num_positions * 3) UP(uvs, desc->num_positions * 2)
+    UP(indices, desc->num_indices * 3) UP(texels, desc->num_texels) UP(tables, desc->num_tables) UP(grid_data, desc->num_grid_data)
+#undef UP
+    d.light_pmf = d.tables + desc->light_pmf_offset;
+    d.light_cdf = d.tables + desc->light_cdf_offset;
+
+    // primitive lists for the BVH builder
+    std::vector<int> tri_shape(desc->num_indices, 0);
+    std::vector<SpherePrim> spheres;
+    for (uint64_t i = 0; i < desc->num_shapes; i++) {
+        const lj_shape &sh = desc->shapes[i];
+        if (sh.kind == LJ_SHAPE_MESH) {
+            for (uint32_t t = 0; t < sh.num_triangles; t++) tri_shape[sh.triangle_offset + t] = (int)i;
+        } else {
+            SpherePrim sp; sp.cx = sh.center[0]; sp.cy = sh.center[1]; sp.cz = sh.center[2]; sp.r = sh.radius; sp.geom = (int)i; sp._pad = 0;
+            spheres.push_back(sp);
+        }
+    }
+    const int *d_tri_shape; const SpherePrim *d_spheres;
+    if ((rc = upload(s, tri_shape.data(), tri_shape.size(), &d_tri_shape)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+    if ((rc = upload(s, spheres.data(), spheres.size(), &d_spheres)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+    cudaEventRecord(e1);
+
+    BvhBuildInput bi;
+    bi.num_tris = (int)desc->num_indices; bi.num_spheres = (int)spheres.size();
+    bi.positions = d.positions; bi.indices = d.indices; bi.tri_shape = d_tri_shape; bi.shapes = d.shapes; bi.spheres = d_spheres;
+    char berr[256] = "";
+    if (lj_bvh_build(bi, s->bvh, berr) != 0) { lj_set_error("BVH build failed: %s", berr); lj_scene_destroy(s); return LJ_ECUDA; }
+    cudaEventRecord(e2);
+    cudaEventSynchronize(e2);
+    d.num_tris = bi.num_tris; d.num_spheres = bi.num_spheres; d.num_prims = s->bvh.num_prims;
+    d.tri_verts = s->bvh.tri_verts; d.spheres = d_spheres;
+    d.bvh2 = s->bvh.bvh2; d.bvh2_root = s->bvh.bvh2_root;
+    d.bvh8 = s->bvh.bvh8;
+    if (s->bvh.bvh8) d.tri_verts = s->bvh.tri_verts8 ? s->bvh.tri_verts8 : s->bvh.tri_verts;
+    float ms = 0;
+    cudaEventElapsedTime(&ms, e0, e1); s->build_stats.upload_ms = ms;
+    cudaEventElapsedTime(&ms, e1, e2); s->build_stats.bvh_build_ms = ms;
+    s->build_stats.bvh_nodes = s->bvh.bvh8 ? s->bvh.num_bvh8 : s->bvh.num_bvh2;
+    s->build_stats.bvh_prims = s->bvh.num_prims;
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
+    *out = s;
+    return LJ_OK;
+}
+
+extern "C" void lj_scene_destroy(lj_scene *s) {
+    if (!s) return;
+    for (void *p : s->allocs) cudaFree(p);
+    lj_bvh_free(s->bvh);
+    if (s->wf_pool) cudaFree(s->wf_pool);
+    delete s;
+}
+
+extern "C" int lj_scene_info(lj_scene *s, int32_t *width, int32_t *height, int32_t *spp, lj_stats *build_stats) {
+    if (!s) { lj_set_error("lj_scene_info: null scene"); return LJ_EINVAL; }
+    if (width) *width = s->d.camera.width;
+    if (height) *height = s->d.camera.height;
+    if (spp) *spp = s->d.options.samples_per_pixel;
+    if (build_stats) *build_stats = s->build_stats;
+    return LJ_OK;
+}
+
+// ---------------- render dispatch (render.cpp:155-170) ----------------
+__global__ void k_finalize(int npix, const double *sum, double inv_spp_num, float *rgb) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix * 3) return;
+    // render.cpp:94: img = radiance / Real(spp)  (vector / scalar = multiply by reciprocal)
+    rgb[i] = (float)(sum[i] * inv_spp_num);
+}
+
+static int make_launch(lj_scene *s, const lj_render_params *params, RenderLaunch &rl) {
+    lj_render_params p;
+    if (params) p = *params; else { memset(&p, 0, sizeof p); p.max_depth_override = -100; p.rng_mode = LJ_RNG_SAMPLE_STREAMS; }
+    rl.p = p;
+    rl.spp = p.spp > 0 ? p.spp : s->d.options.samples_per_pixel;
+    rl.s_begin = 0; rl.s_end = rl.spp;
+    if (p.sample_end > p.sample_begin) { rl.s_begin = p.sample_begin; rl.s_end = p.sample_end; }
+    if (rl.spp <= 0) { lj_set_error("render: spp must be positive"); return LJ_EINVAL; }
+    if (p.tile_world < 0 || (p.tile_world > 0 && (p.tile_rank < 0 || p.tile_rank >= p.tile_world))) { lj_set_error("render: bad tile partition %d/%d", p.tile_rank, p.tile_world); return LJ_EINVAL; }
+    rl.width = s->d.camera.width; rl.height = s->d.camera.height;
+    rl.ntx = (rl.width + 15) / 16; rl.nty = (rl.height + 15) / 16;
+    return LJ_OK;
+}
+
+extern "C" int lj_render_device(lj_scene *s, const lj_render_params *params, double *dev_sum, lj_stats *stats) {
+    if (!s || !dev_sum) { lj_set_error("lj_render_device: null argument"); return LJ_EINVAL; }
+    LJ_CUDA(cudaSetDevice(s->ctx->device));
+    RenderLaunch rl;
+    int rc = make_launch(s, params, rl);
+    if (rc) return rc;
+    lj_stats st; memset(&st, 0, sizeof st);
+    st.upload_ms = s->build_stats.upload_ms; st.bvh_build_ms = s->build_stats.bvh_build_ms;
+    st.bvh_nodes = s->build_stats.bvh_nodes; st.bvh_prims = s->build_stats.bvh_prims;
+    DScene saved = s->d;
+    if (rl.p.max_depth_override != -100) s->d.options.max_depth = rl.p.max_depth_override;
+    cudaEvent_t e0, e1; cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0);
+    int integ = s->d.options.integrator;
+    if (integ == LJ_INTEGRATOR_PATH) {
+        if (rl.p.rng_mode == LJ_RNG_TILE_STREAMS) rc = lj_render_tiles_mode_a(s, rl, dev_sum, &st);
+        else if (rl.p.engine == LJ_ENGINE_MEGAKERNEL) rc = lj_render_megakernel(s, rl, dev_sum, &st);
+        else rc = lj_render_wavefront(s, rl, dev_sum, &st);
+    } else if (integ == LJ_INTEGRATOR_VOLPATH) {
+        rc = lj_render_volpath(s, rl, dev_sum, &st);
+    } else {
+        rc = lj_render_aux(s, rl, dev_sum, &st);
+    }
+    cudaEventRecord(e1);
+    cudaError_t ce = cudaEventSynchronize(e1);
+    s->d = saved;
+    if (rc == LJ_OK && ce != cudaSuccess) { lj_set_error("render kernels failed: %s", cudaGetErrorString(ce)); rc = LJ_ECUDA; }
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    st.render_ms = ms;
+    if (stats) *stats = st;
+    return rc;
+}
+
+extern "C" int lj_render(lj_scene *s, const lj_render_params *params, float *rgb_out, lj_stats *stats) {
+    if (!s || !rgb_out) { lj_set_error("lj_render: null argument"); return LJ_EINVAL; }
+    LJ_CUDA(cudaSetDevice(s->ctx->device));
+    int npix = s->d.camera.width * s->d.camera.height;
+    double *sum = nullptr; float *rgb = nullptr;
+    LJ_CUDA(cudaMalloc(&sum, sizeof(double) * 3 * (size_t)npix));
+    LJ_CUDA(cudaMalloc(&rgb, sizeof(float) * 3 * (size_t)npix));
+    int rc = lj_render_device(s, params, sum, stats);
+    if (rc == LJ_OK) {
+        RenderLaunch rl; make_launch(s, params, rl);
+        int integ = s->d.options.integrator;
+        double denom = (integ == LJ_INTEGRATOR_PATH || integ == LJ_INTEGRATOR_VOLPATH) ? (double)(rl.s_end - rl.s_begin) : 1.0;
+        k_finalize<<<(npix * 3 + 255) / 256, 256>>>(npix, sum, 1.0 / denom, rgb);
+        cudaError_t e = cudaMemcpy(rgb_out, rgb, sizeof(float) * 3 * (size_t)npix, cudaMemcpyDeviceToHost);
+        if (e != cudaSuccess) { lj_set_error("lj_render: D2H failed: %s", cudaGetErrorString(e)); rc = LJ_ECUDA; }
+    }
+    cudaFree(sum); cudaFree(rgb);
+    return rc;
+}
+
+// ---------------- batch ray casting (rtcIntersect1 / rtcOccluded1) ----------------
+__global__ void k_intersect_batch(DScene sc, const lj_ray *rays, long long n, lj_hit *hits, int any_hit) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    lj_ray r = rays[i];
+    RayF rf; rf.ox = r.org[0]; rf.oy = r.org[1]; rf.oz = r.org[2]; rf.tnear = r.tnear;
+    rf.dx = r.dir[0]; rf.dy = r.dir[1]; rf.dz = r.dir[2]; rf.tfar = r.tfar;
+    lj_hit out; out.t = r.tfar; out.u = out.v = 0; out.geom_id = -1; out.prim_id = -1; out.ng[0] = out.ng[1] = out.ng[2] = 0;
+    if (any_hit) {
+        if (trace_any(sc, rf)) { out.t = -INFINITY; out.geom_id = 0; }
+    } else {
+        Hit h;
+        if (trace_closest(sc, rf, &h)) {
+            out.t = h.t; out.u = h.u; out.v = h.v; out.geom_id = h.geom; out.prim_id = h.prim;
+            out.ng[0] = h.ngx; out.ng[1] = h.ngy; out.ng[2] = h.ngz;
+        }
+    }
+    hits[i] = out;
+}
+
+extern "C" int lj_intersect_batch(lj_scene *s, const lj_ray *rays, int64_t n, lj_hit *hits, int any_hit) {
+    if (!s || (n > 0 && (!rays || !hits))) { lj_set_error("lj_intersect_batch: null argument"); return LJ_EINVAL; }
+    if (n <= 0) return LJ_OK;
+    LJ_CUDA(cudaSetDevice(s->ctx->device));
+    lj_ray *dr = nullptr; lj_hit *dh = nullptr;
+    LJ_CUDA(cudaMalloc(&dr, sizeof(lj_ray) * n));
+    LJ_CUDA(cudaMalloc(&dh, sizeof(lj_hit) * n));
+    cudaMemcpy(dr, rays, sizeof(lj_ray) * n, cudaMemcpyHostToDevice);
+    k_intersect_batch<<<(unsigned)((n + 127) / 128), 128>>>(s->d, dr, n, dh, any_hit);
+    cudaError_t e = cudaMemcpy(hits, dh, sizeof(lj_hit) * n, cudaMemcpyDeviceToHost);
+    cudaFree(dr); cudaFree(dh);
+    if (e != cudaSuccess) { lj_set_error("lj_intersect_batch: %s", cudaGetErrorString(e)); return LJ_ECUDA; }
+    return LJ_OK;
+}

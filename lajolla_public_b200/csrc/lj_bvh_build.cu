@@ -1,0 +1,244 @@
+// GPU BVH construction: replaces Embree's rtcCommitScene
+// (/root/reference/src/scene.cpp:20-27).  Pipeline, all on the device:
+//   1. primitive bounds in f32 from the f64 scene arrays (the reference hands
+//      Embree float vertices, shapes/triangle_mesh.inl:11-14, and float sphere
+//      bounds, shapes/sphere.inl:1-10) + scene AABB reduction
+//   2. 63-bit Morton codes of the centroids, radix sort (cub::DeviceRadixSort)
+//   3. binary radix tree (Karras 2012), bottom-up AABB fit
+//   4. collapse to an 8-wide tree and quantise into 80-byte nodes (Ylitie 2017)
+#include "lj_bvh_build.h"
+
+#include <cub/device/device_radix_sort.cuh>
+#include <cfloat>
+#include <cstdio>
+#include <vector>
+
+#define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { snprintf(err, 256, "%s: %s", #x, cudaGetErrorString(e_)); return -1; } } while (0)
+
+namespace {
+
+__device__ __forceinline__ void atomic_min_f(float *addr, float v) {
+    // order-preserving int mapping for floats
+    if (v >= 0) atomicMin((int *)addr, __float_as_int(v)); else atomicMax((unsigned *)addr, __float_as_uint(v));
+}
+__device__ __forceinline__ void atomic_max_f(float *addr, float v) {
+    if (v >= 0) atomicMax((int *)addr, __float_as_int(v)); else atomicMin((unsigned *)addr, __float_as_uint(v));
+}
+
+// prim i < num_tris: triangle i (global index into `indices`); else sphere i - num_tris
+__global__ void k_prim_bounds(int num_tris, int num_spheres, const double *positions, const int *indices,
+                              const int *tri_shape, const lj_shape *shapes, const SpherePrim *spheres,
+                              float4 *prim_lo, float4 *prim_hi, float *scene_bounds /* lo[3], hi[3] */) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    int n = num_tris + num_spheres;
+    float lo[3] = {FLT_MAX, FLT_MAX, FLT_MAX}, hi[3] = {-FLT_MAX, -FLT_MAX, -FLT_MAX};
+    if (i < n) {
+        if (i < num_tris) {
+            const lj_shape &s = shapes[tri_shape[i]];
+            for (int k = 0; k < 3; k++) {
+                size_t v = (size_t)s.vertex_offset + indices[3 * (size_t)i + k];
+                for (int a = 0; a < 3; a++) {
+                    float f = (float)positions[3 * v + a];
+                    lo[a] = fminf(lo[a], f); hi[a] = fmaxf(hi[a], f);
+                }
+            }
+        } else {
+            const SpherePrim &s = spheres[i - num_tris];
+            lo[0] = (float)(s.cx - s.r); lo[1] = (float)(s.cy - s.r); lo[2] = (float)(s.cz - s.r);
+            hi[0] = (float)(s.cx + s.r); hi[1] = (float)(s.cy + s.r); hi[2] = (float)(s.cz + s.r);
+        }
+        prim_lo[i] = make_float4(lo[0], lo[1], lo[2], 0.f);
+        prim_hi[i] = make_float4(hi[0], hi[1], hi[2], 0.f);
+    }
+    // warp reduce, then one atomic per warp
+    for (int a = 0; a < 3; a++) {
+        float l = lo[a], h = hi[a];
+        for (int o = 16; o > 0; o >>= 1) {
+            l = fminf(l, __shfl_xor_sync(0xffffffffu, l, o));
+            h = fmaxf(h, __shfl_xor_sync(0xffffffffu, h, o));
+        }
+        if ((threadIdx.x & 31) == 0 && l <= h) { atomic_min_f(&scene_bounds[a], l); atomic_max_f(&scene_bounds[3 + a], h); }
+    }
+}
+
+__device__ __forceinline__ unsigned long long expand21(unsigned long long v) {
+    v &= 0x1fffffULL;
+    v = (v | v << 32) & 0x1f00000000ffffULL;
+    v = (v | v << 16) & 0x1f0000ff0000ffULL;
+    v = (v | v << 8) & 0x100f00f00f00f00fULL;
+    v = (v | v << 4) & 0x10c30c30c30c30c3ULL;
+    v = (v | v << 2) & 0x1249249249249249ULL;
+    return v;
+}
+
+__global__ void k_morton(int n, const float4 *prim_lo, const float4 *prim_hi, const float *scene_bounds,
+                         unsigned long long *keys, int *vals) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    float4 lo = prim_lo[i], hi = prim_hi[i];
+    float c[3] = {0.5f * (lo.x + hi.x), 0.5f * (lo.y + hi.y), 0.5f * (lo.z + hi.z)};
+    unsigned long long q[3];
+    for (int a = 0; a < 3; a++) {
+        float ext = scene_bounds[3 + a] - scene_bounds[a];
+        float t = ext > 0 ? (c[a] - scene_bounds[a]) / ext : 0.f;
+        t = fminf(fmaxf(t, 0.f), 1.f);
+        q[a] = (unsigned long long)fminf(t * 2097152.f, 2097151.f);
+    }
+    keys[i] = (expand21(q[0]) << 2) | (expand21(q[1]) << 1) | expand21(q[2]);
+    vals[i] = i;
+}
+
+__device__ __forceinline__ int delta(const unsigned long long *keys, int n, int i, int j) {
+    if (j < 0 || j >= n) return -1;
+    unsigned long long a = keys[i], b = keys[j];
+    if (a == b) return 64 + __clz(i ^ j);
+    return __clzll((long long)(a ^ b));
+}
+
+// Karras 2012: internal node i covers a key range; children are internal nodes or leaves.
+__global__ void k_radix_tree(int n, const unsigned long long *keys, int *left, int *right, int *parent_inner, int *parent_leaf) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int d = (delta(keys, n, i, i + 1) - delta(keys, n, i, i - 1)) >= 0 ? 1 : -1;
+    int dmin = delta(keys, n, i, i - d);
+    int lmax = 2;
+    while (delta(keys, n, i, i + lmax * d) > dmin) lmax <<= 1;
+    int l = 0;
+    for (int t = lmax >> 1; t >= 1; t >>= 1)
+        if (delta(keys, n, i, i + (l + t) * d) > dmin) l += t;
+    int j = i + l * d;
+    int dnode = delta(keys, n, i, j);
+    int s = 0;
+    int t = l;
+    do {
+        t = (t + 1) >> 1;
+        if (delta(keys, n, i, i + (s + t) * d) > dnode) s += t;
+    } while (t > 1);
+    int gamma = i + s * d + min(d, 0);
+    int lo = min(i, j), hi = max(i, j);
+    int lc, rc;
+    if (lo == gamma) { lc = ~gamma; parent_leaf[gamma] = i; } else { lc = gamma; parent_inner[gamma] = i; }
+    if (hi == gamma + 1) { rc = ~(gamma + 1); parent_leaf[gamma + 1] = i; } else { rc = gamma + 1; parent_inner[gamma + 1] = i; }
+    left[i] = lc; right[i] = rc;
+    if (i == 0) parent_inner[0] = -1;
+}
+
+// bottom-up AABB fit; second arriving thread at a node continues upward
+__global__ void k_fit(int n, const int *vals, const float4 *prim_lo, const float4 *prim_hi, const int *left, const int *right,
+                      const int *parent_inner, const int *parent_leaf, int *flags, float4 *node_lo, float4 *node_hi) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int node = parent_leaf[i];
+    while (node >= 0) {
+        if (atomicAdd(&flags[node], 1) == 0) return;
+        __threadfence();
+        int lc = left[node], rc = right[node];
+        float4 llo = lc < 0 ? prim_lo[vals[~lc]] : __ldcg(&node_lo[lc]);
+        float4 lhi = lc < 0 ? prim_hi[vals[~lc]] : __ldcg(&node_hi[lc]);
+        float4 rlo = rc < 0 ? prim_lo[vals[~rc]] : __ldcg(&node_lo[rc]);
+        float4 rhi = rc < 0 ? prim_hi[vals[~rc]] : __ldcg(&node_hi[rc]);
+        node_lo[node] = make_float4(fminf(llo.x, rlo.x), fminf(llo.y, rlo.y), fminf(llo.z, rlo.z), 0.f);
+        node_hi[node] = make_float4(fmaxf(lhi.x, rhi.x), fmaxf(lhi.y, rhi.y), fmaxf(lhi.z, rhi.z), 0.f);
+        __threadfence();
+        node = parent_inner[node];
+    }
+}
+
+__global__ void k_emit_bvh2(int n, const int *left, const int *right, const float4 *node_lo, const float4 *node_hi, Bvh2Node *out) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    Bvh2Node nd;
+    float4 lo = node_lo[i], hi = node_hi[i];
+    nd.lo[0] = lo.x; nd.lo[1] = lo.y; nd.lo[2] = lo.z; nd.left = left[i];
+    nd.hi[0] = hi.x; nd.hi[1] = hi.y; nd.hi[2] = hi.z; nd.right = right[i];
+    out[i] = nd;
+}
+
+// primitive slots in leaf (sorted) order: 3 float4 each
+__global__ void k_emit_prims(int n, int num_tris, const int *vals, const double *positions, const int *indices,
+                             const int *tri_shape, const lj_shape *shapes, const SpherePrim *spheres, float4 *tri_verts) {
+    int slot = blockIdx.x * blockDim.x + threadIdx.x;
+    if (slot >= n) return;
+    int i = vals[slot];
+    if (i < num_tris) {
+        int sid = tri_shape[i];
+        const lj_shape &s = shapes[sid];
+        float p[9];
+        for (int k = 0; k < 3; k++) {
+            size_t v = (size_t)s.vertex_offset + indices[3 * (size_t)i + k];
+            for (int a = 0; a < 3; a++) p[3 * k + a] = (float)positions[3 * v + a];
+        }
+        tri_verts[3 * slot + 0] = make_float4(p[0], p[1], p[2], __int_as_float(sid));
+        tri_verts[3 * slot + 1] = make_float4(p[3], p[4], p[5], __int_as_float(i - (int)s.triangle_offset));
+        tri_verts[3 * slot + 2] = make_float4(p[6], p[7], p[8], __int_as_float(0));
+    } else {
+        int si = i - num_tris;
+        tri_verts[3 * slot + 0] = make_float4(__int_as_float(si), 0.f, 0.f, __int_as_float(spheres[si].geom));
+        tri_verts[3 * slot + 1] = make_float4(0.f, 0.f, 0.f, __int_as_float(0));
+        tri_verts[3 * slot + 2] = make_float4(0.f, 0.f, 0.f, __int_as_float(1));
+    }
+}
+
+} // namespace
+
+int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
+    const int n = in.num_tris + in.num_spheres;
+    memset(&out, 0, sizeof out);
+    out.num_prims = n;
+    if (n == 0) return 0;
+    const int B = 256;
+    const int G = (n + B - 1) / B;
+    float4 *prim_lo = nullptr, *prim_hi = nullptr, *node_lo = nullptr, *node_hi = nullptr;
+    float *bounds = nullptr;
+    unsigned long long *keys = nullptr, *keys2 = nullptr;
+    int *vals = nullptr, *vals2 = nullptr, *left = nullptr, *right = nullptr, *par_i = nullptr, *par_l = nullptr, *flags = nullptr;
+    void *tmp = nullptr;
+    CK(cudaMalloc(&prim_lo, sizeof(float4) * n)); CK(cudaMalloc(&prim_hi, sizeof(float4) * n));
+    CK(cudaMalloc(&bounds, sizeof(float) * 6));
+    float init_b[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
+    CK(cudaMemcpy(bounds, init_b, sizeof init_b, cudaMemcpyHostToDevice));
+    k_prim_bounds<<<G, B>>>(in.num_tris, in.num_spheres, in.positions, in.indices, in.tri_shape, in.shapes, in.spheres, prim_lo, prim_hi, bounds);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out.lo, bounds, sizeof(float) * 3, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(out.hi, bounds + 3, sizeof(float) * 3, cudaMemcpyDeviceToHost));
+
+    CK(cudaMalloc(&keys, 8 * (size_t)n)); CK(cudaMalloc(&keys2, 8 * (size_t)n));
+    CK(cudaMalloc(&vals, 4 * (size_t)n)); CK(cudaMalloc(&vals2, 4 * (size_t)n));
+    k_morton<<<G, B>>>(n, prim_lo, prim_hi, bounds, keys, vals);
+    CK(cudaGetLastError());
+    size_t tmp_bytes = 0;
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
+    CK(cudaMalloc(&tmp, tmp_bytes));
+    CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
+
+    CK(cudaMalloc(&out.tri_verts, sizeof(float4) * 3 * (size_t)n));
+    k_emit_prims<<<G, B>>>(n, in.num_tris, vals2, in.positions, in.indices, in.tri_shape, in.shapes, in.spheres, out.tri_verts);
+    CK(cudaGetLastError());
+
+    if (n >= 2) {
+        CK(cudaMalloc(&left, 4 * (size_t)n)); CK(cudaMalloc(&right, 4 * (size_t)n));
+        CK(cudaMalloc(&par_i, 4 * (size_t)n)); CK(cudaMalloc(&par_l, 4 * (size_t)n));
+        CK(cudaMalloc(&flags, 4 * (size_t)n)); CK(cudaMemset(flags, 0, 4 * (size_t)n));
+        CK(cudaMalloc(&node_lo, sizeof(float4) * n)); CK(cudaMalloc(&node_hi, sizeof(float4) * n));
+        k_radix_tree<<<G, B>>>(n, keys2, left, right, par_i, par_l);
+        CK(cudaGetLastError());
+        k_fit<<<G, B>>>(n, vals2, prim_lo, prim_hi, left, right, par_i, par_l, flags, node_lo, node_hi);
+        CK(cudaGetLastError());
+        CK(cudaMalloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
+        k_emit_bvh2<<<G, B>>>(n, left, right, node_lo, node_hi, out.bvh2);
+        CK(cudaGetLastError());
+        out.bvh2_root = 0;
+        out.num_bvh2 = n - 1;
+    }
+    CK(cudaDeviceSynchronize());
+    // the 8-wide collapse consumes the binary tree (lj_bvh8_build.cu)
+    int rc = lj_bvh8_collapse(n, out.bvh2, out.tri_verts, left, right, node_lo, node_hi, vals2, prim_lo, prim_hi, out, err);
+    cudaFree(prim_lo); cudaFree(prim_hi); cudaFree(bounds); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
+    cudaFree(left); cudaFree(right); cudaFree(par_i); cudaFree(par_l); cudaFree(flags); cudaFree(node_lo); cudaFree(node_hi); cudaFree(tmp);
+    return rc;
+}
+
+void lj_bvh_free(BvhBuildOutput &out) {
+    cudaFree(out.tri_verts); cudaFree(out.bvh2); cudaFree(out.bvh8); cudaFree(out.tri_verts8);
+    memset(&out, 0, sizeof out);
+}

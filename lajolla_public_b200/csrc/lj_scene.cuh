@@ -1,0 +1,83 @@
+// Device-resident scene: the lj_scene_desc arrays copied to HBM plus the GPU-built BVH.
+#pragma once
+#include "lj_math.cuh"
+#include "../../include/lajolla_gpu.h"
+
+// ---- BVH ----
+// Binary LBVH node (build intermediate and the simple traversal path), 32 bytes.
+struct __align__(16) Bvh2Node {
+    float lo[3]; int left;     // left  >= 0: inner child index; < 0: leaf, prim = ~left
+    float hi[3]; int right;
+};
+
+// Compressed 8-wide node, 80 bytes = five 16-byte loads (layout after Ylitie, Karras,
+// Laine 2017 "Efficient Incoherent Ray Traversal on GPUs Through Compressed Wide BVHs").
+struct __align__(16) Bvh8Node {
+    float px, py, pz;          // quantisation origin
+    uint8_t ex, ey, ez, imask; // per-axis exponent, bit i set => child i is an inner node
+    uint32_t child_base;       // index of first inner child (children are contiguous)
+    uint32_t prim_base;        // index of first primitive referenced by this node
+    uint8_t meta[8];           // inner: (1<<5)|(24+slot) ; leaf: (unary count << 5) | offset ; empty: 0
+    uint8_t qlox[8], qloy[8], qloz[8];
+    uint8_t qhix[8], qhiy[8], qhiz[8];
+};
+static_assert(sizeof(Bvh8Node) == 80, "Bvh8Node must be 80 bytes");
+
+// A sphere as a BVH primitive (shapes/sphere.inl: one user primitive per sphere)
+struct SpherePrim { double cx, cy, cz, r; int geom; int _pad; };
+
+struct DScene {
+    lj_camera camera;
+    lj_options options;
+    double bounds_radius;
+    double eps;                 // get_shadow_epsilon == get_intersection_epsilon, scene.h:99-105
+    int envmap_light_id;
+    int num_lights, num_shapes, num_materials;
+
+    const lj_shape *shapes;
+    const lj_light *lights;
+    const lj_material *materials;
+    const lj_medium *media;
+    const lj_texture *textures;
+    const lj_image *images1, *images3;
+    const double *positions, *normals, *uvs;
+    const int *indices;
+    const double *texels, *tables, *grid_data;
+    const double *light_pmf, *light_cdf;
+
+    // ray casting structures (f32, the Embree seam of intersection.cpp:15-24)
+    int num_tris, num_spheres, num_prims;
+    const float4 *tri_verts;    // 3 float4 per primitive slot in BVH leaf order: (v0, geom) (v1, prim) (v2, kind)
+    const SpherePrim *spheres;
+    const Bvh2Node *bvh2; int bvh2_root;
+    const Bvh8Node *bvh8;
+};
+
+// intersection.h:15-35
+struct PathVertex {
+    d3 position, geometry_normal;
+    Frame shading_frame;
+    d2 st, uv;
+    double uv_screen_size, mean_curvature, ray_radius;
+    int shape_id, primitive_id, material_id, interior_medium_id, exterior_medium_id;
+};
+
+struct Ray { d3 org, dir; double tnear, tfar; };                 // ray.h:9-12
+struct RayDiff { double radius, spread; };                       // ray.h:27-31
+struct PointAndNormal { d3 position, normal; };                  // point_and_normal.h:9-12
+
+// What crosses the ray-cast seam back (RTCRay.tfar + RTCHit, all f32 / u32)
+struct Hit { float t, u, v; int geom, prim; float ngx, ngy, ngz; };
+
+LJ_D RayDiff init_ray_differential(int w, int h) { RayDiff r; r.radius = 0; r.spread = 0.25 / (w > h ? w : h); return r; }
+LJ_D double rd_transfer(const RayDiff &r, double dist) { return r.radius + r.spread * dist; }
+LJ_D double rd_reflect(const RayDiff &r, double mean_curvature, double roughness) {
+    double spec_spread = r.spread + 2 * mean_curvature * r.radius;
+    double diff_spread = 0.2;
+    return fmax(spec_spread * (1 - roughness) + diff_spread * roughness, 0.0);
+}
+LJ_D double rd_refract(const RayDiff &r, double mean_curvature, double eta, double roughness) {
+    double spec_spread = (r.spread + 2 * mean_curvature * r.radius) / eta;
+    double diff_spread = 0.2;
+    return fmax(spec_spread * (1 - roughness) + diff_spread * roughness, 0.0);
+}
