@@ -1,0 +1,197 @@
+"""ctypes binding of include/lajolla_gpu.h (the drop-in boundary for
+`Image3 render(const Scene&)`, /root/reference/src/render.h:9)."""
+import ctypes as C
+import os
+import numpy as np
+
+RNG_TILE_STREAMS = 0     # mode A: render.cpp:82 per-tile pcg32 streams (tile-serial)
+RNG_SAMPLE_STREAMS = 1   # mode B: per-(pixel,sample) streams
+ENGINE_WAVEFRONT = 0
+ENGINE_MEGAKERNEL = 1
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+
+
+class LjError(RuntimeError):
+    pass
+
+
+def lib_path():
+    return os.path.join(_HERE, "liblajolla_b200.so")
+
+
+class RenderParams(C.Structure):
+    _fields_ = [("spp", C.c_int32), ("rng_mode", C.c_int32), ("engine", C.c_int32),
+                ("sample_begin", C.c_int32), ("sample_end", C.c_int32),
+                ("tile_rank", C.c_int32), ("tile_world", C.c_int32),
+                ("max_depth_override", C.c_int32), ("paths_in_flight", C.c_int32), ("flags", C.c_int32)]
+
+    def __init__(self, **kw):
+        super().__init__()
+        self.max_depth_override = -100
+        self.rng_mode = RNG_SAMPLE_STREAMS
+        for k, v in kw.items():
+            setattr(self, k, v)
+
+
+class Stats(C.Structure):
+    _fields_ = [("render_ms", C.c_double), ("upload_ms", C.c_double), ("bvh_build_ms", C.c_double),
+                ("samples", C.c_uint64), ("rays_primary", C.c_uint64), ("rays_extension", C.c_uint64),
+                ("rays_shadow", C.c_uint64), ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64),
+                ("kernel_launches", C.c_uint64), ("extend_ms", C.c_double), ("shadow_ms", C.c_double),
+                ("shade_ms", C.c_double), ("generate_ms", C.c_double), ("bvh_nodes", C.c_uint64),
+                ("bvh_prims", C.c_uint64)]
+
+    @property
+    def rays(self):
+        return self.rays_primary + self.rays_extension + self.rays_shadow
+
+    def as_dict(self):
+        return {n: getattr(self, n) for n, _ in self._fields_}
+
+
+class Ray(C.Structure):
+    _fields_ = [("org", C.c_float * 3), ("tnear", C.c_float), ("dir", C.c_float * 3), ("tfar", C.c_float)]
+
+
+class Hit(C.Structure):
+    _fields_ = [("t", C.c_float), ("u", C.c_float), ("v", C.c_float), ("geom_id", C.c_int32),
+                ("prim_id", C.c_int32), ("ng", C.c_float * 3)]
+
+
+RAY_DTYPE = np.dtype([("org", "<f4", 3), ("tnear", "<f4"), ("dir", "<f4", 3), ("tfar", "<f4")])
+HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("geom_id", "<i4"), ("prim_id", "<i4"), ("ng", "<f4", 3)])
+
+# every symbol include/lajolla_gpu.h declares
+ABI_SYMBOLS = ["lj_init", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", "lj_render", "lj_render_device",
+               "lj_intersect_batch", "lj_scene_info", "lj_last_error", "lj_scene_desc_save", "lj_scene_desc_load",
+               "lj_scene_desc_free"]
+
+_lib = None
+
+
+def load_library():
+    """dlopen liblajolla_b200.so; fails loudly if it has not been built (no fallback)."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    p = lib_path()
+    if not os.path.exists(p):
+        raise LjError(f"{p} is missing: build it with `make -C lajolla_public_b200` "
+                      "(or __graft_entry__.build()); there is no CPU fallback")
+    lib = C.CDLL(p)
+    lib.lj_last_error.restype = C.c_char_p
+    lib.lj_init.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.lj_shutdown.argtypes = [C.c_void_p]
+    lib.lj_shutdown.restype = None
+    lib.lj_scene_create.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
+    lib.lj_scene_destroy.argtypes = [C.c_void_p]
+    lib.lj_scene_destroy.restype = None
+    lib.lj_render.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.POINTER(Stats)]
+    lib.lj_render_device.argtypes = [C.c_void_p, C.POINTER(RenderParams), C.c_void_p, C.POINTER(Stats)]
+    lib.lj_intersect_batch.argtypes = [C.c_void_p, C.c_void_p, C.c_int64, C.c_void_p, C.c_int]
+    lib.lj_scene_info.argtypes = [C.c_void_p, C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(C.c_int32), C.POINTER(Stats)]
+    lib.lj_scene_desc_save.argtypes = [C.c_void_p, C.c_char_p]
+    lib.lj_scene_desc_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
+    lib.lj_scene_desc_free.argtypes = [C.c_void_p]
+    lib.lj_scene_desc_free.restype = None
+    _lib = lib
+    return lib
+
+
+def _check(lib, rc, what):
+    if rc != 0:
+        raise LjError(f"{what} failed ({rc}): {lib.lj_last_error().decode(errors='replace')}")
+
+
+class LajollaGPU:
+    """One context per CUDA device (lj_init / lj_shutdown)."""
+
+    def __init__(self, device=0):
+        self.lib = load_library()
+        self.handle = C.c_void_p()
+        _check(self.lib, self.lib.lj_init(int(device), C.byref(self.handle)), "lj_init")
+        self.device = device
+
+    def load_scene(self, blob_path, res=None, spp=None):
+        return Scene(self, blob_path, res=res, spp=spp)
+
+    def close(self):
+        if self.handle:
+            self.lib.lj_shutdown(self.handle)
+            self.handle = C.c_void_p()
+
+
+class Scene:
+    """A flattened scene blob (.ljs, written by bin/lj_flatten or LJ_SAVE_SCENE) resident on the GPU."""
+
+    def __init__(self, gpu, blob_path, res=None, spp=None):
+        self.gpu = gpu
+        lib = gpu.lib
+        desc = C.c_void_p()
+        _check(lib, lib.lj_scene_desc_load(os.fsencode(blob_path), C.byref(desc)), "lj_scene_desc_load")
+        if res is not None:   # film-size override (lj_camera.width/height follow the two 4x4 f64 matrices)
+            wh = (C.c_int32 * 2).from_address(desc.value + 256)
+            wh[0], wh[1] = int(res[0]), int(res[1])
+        if spp is not None:   # lj_options.samples_per_pixel
+            opt = (C.c_int32 * 6).from_address(desc.value + 256 + 16 + 8)
+            opt[1] = int(spp)
+        self.handle = C.c_void_p()
+        try:
+            _check(lib, lib.lj_scene_create(gpu.handle, desc, C.byref(self.handle)), "lj_scene_create")
+        finally:
+            lib.lj_scene_desc_free(desc)
+        w, h, spp = C.c_int32(), C.c_int32(), C.c_int32()
+        self.build_stats = Stats()
+        _check(lib, lib.lj_scene_info(self.handle, C.byref(w), C.byref(h), C.byref(spp), C.byref(self.build_stats)), "lj_scene_info")
+        self.width, self.height, self.spp = w.value, h.value, spp.value
+
+    def render(self, params=None, out=None):
+        """render(): host f32 image (h, w, 3), y=0 top.  `out` may be a pinned/host f32 array to fill."""
+        lib = self.gpu.lib
+        params = params or RenderParams()
+        if out is None:
+            out = np.empty((self.height, self.width, 3), dtype=np.float32)
+        assert out.dtype == np.float32 and out.size == self.height * self.width * 3 and out.flags["C_CONTIGUOUS"]
+        st = Stats()
+        _check(lib, lib.lj_render(self.handle, C.byref(params), out.ctypes.data_as(C.c_void_p), C.byref(st)), "lj_render")
+        return out, st
+
+    def render_into_device(self, dev_ptr, params=None):
+        """render radiance SUMS (f64, h*w*3) into caller-owned device memory (e.g. a torch tensor's data_ptr())."""
+        lib = self.gpu.lib
+        params = params or RenderParams()
+        st = Stats()
+        _check(lib, lib.lj_render_device(self.handle, C.byref(params), C.c_void_p(int(dev_ptr)), C.byref(st)), "lj_render_device")
+        return st
+
+    def intersect(self, rays, any_hit=False):
+        """rtcIntersect1 / rtcOccluded1 for a batch: rays is a RAY_DTYPE array; returns a HIT_DTYPE array."""
+        rays = np.ascontiguousarray(rays, dtype=RAY_DTYPE)
+        hits = np.zeros(rays.shape[0], dtype=HIT_DTYPE)
+        lib = self.gpu.lib
+        _check(lib, lib.lj_intersect_batch(self.handle, rays.ctypes.data_as(C.c_void_p), rays.shape[0],
+                                           hits.ctypes.data_as(C.c_void_p), 1 if any_hit else 0), "lj_intersect_batch")
+        return hits
+
+    def close(self):
+        if self.handle:
+            self.gpu.lib.lj_scene_destroy(self.handle)
+            self.handle = C.c_void_p()
+
+
+def read_pfm(path):
+    """PFM as written by the reference's imwrite (image.cpp:139-149): rows top to bottom, scale -1."""
+    with open(path, "rb") as f:
+        assert f.readline().strip() == b"PF"
+        w, h = map(int, f.readline().split())
+        scale = float(f.readline())
+        data = np.frombuffer(f.read(), dtype="<f4" if scale < 0 else ">f4")
+    return data.reshape(h, w, 3).astype(np.float32)
+
+
+def write_pfm(path, img):
+    img = np.ascontiguousarray(img, dtype="<f4")
+    with open(path, "wb") as f:
+        f.write(b"PF\n%d %d\n-1\n" % (img.shape[1], img.shape[0]))
+        f.write(img.tobytes())

@@ -14,6 +14,8 @@
 //                init_pcg32(s*w*h + y*w + x).  This is the stream layout of
 //                the GPU wavefront renderer; it lets the GPU be compared with
 //                the reference path by path without serialising a tile.
+//       --res W H overrides the film size only (camera matrices untouched); used to
+//       mint small goldens.  The same override exists in lj_flatten.
 //   ref_driver hits <scene.xml> -o hits.bin
 //       primary-ray closest hits through the reference's intersect() for the
 //       pixel-centre ray of every pixel (aux_render's ray, render.cpp:27):
@@ -83,7 +85,7 @@ static Image3 render_mode_b(const Scene &scene, int s_begin, int s_end) {
 static int cmd_render(int argc, char **argv) {
     std::string scene_file, out = "out.pfm", mode = "A", stats_file;
     int spp = -1, threads = std::thread::hardware_concurrency();
-    int s_begin = 0, s_end = -1, max_depth = -100;
+    int s_begin = 0, s_end = -1, max_depth = -100, res_w = 0, res_h = 0;
     for (int i = 2; i < argc; i++) {
         std::string a = argv[i];
         if (a == "-o") out = argv[++i];
@@ -93,6 +95,7 @@ static int cmd_render(int argc, char **argv) {
         else if (a == "--stats") stats_file = argv[++i];
         else if (a == "--sample-range") { s_begin = atoi(argv[++i]); s_end = atoi(argv[++i]); }
         else if (a == "--max-depth") max_depth = atoi(argv[++i]);
+        else if (a == "--res") { res_w = atoi(argv[++i]); res_h = atoi(argv[++i]); }
         else scene_file = a;
     }
     char cwd[4096]; if (!getcwd(cwd, sizeof cwd)) return 2;
@@ -105,6 +108,7 @@ static int cmd_render(int argc, char **argv) {
     Scene scene = parse_scene(scene_file, dev); // chdir()s into the scene folder (parse_scene.cpp:1143)
     if (spp > 0) scene.options.samples_per_pixel = spp;
     if (max_depth != -100) scene.options.max_depth = max_depth;
+    if (res_w > 0) { scene.camera.width = res_w; scene.camera.height = res_h; }  // test-size override (film size only)
     auto t1 = std::chrono::steady_clock::now();
     lj_shim_reset_ray_counts();
     Image3 img;

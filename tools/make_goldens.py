@@ -1,0 +1,71 @@
+#!/usr/bin/env python
+"""Mint test fixtures from the oracle (reference sources + BVH shim), in the authoring
+container (needs /root/reference, oracle/_ref/ref_driver and lajolla_public_b200/bin/lj_flatten).
+
+For every case:  <name>.ljs   flattened scene blob (reference parser -> lj_scene_desc)
+                 <name>_<mode><spp>.npy   oracle image, float32 (h, w, 3)
+Small fixtures go to tests/golden/ (committed); big ones (textures, grids) to scenes_flat/
+(git-ignored, but it travels to the GPU box with gpurun).
+"""
+import json
+import os
+import subprocess
+import sys
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+REF = os.environ.get("LJ_REFERENCE", "/root/reference")
+DRIVER = os.path.join(ROOT, "oracle/_ref/ref_driver")
+FLATTEN = os.path.join(ROOT, "lajolla_public_b200/bin/lj_flatten")
+sys.path.insert(0, ROOT)
+from lajolla_public_b200.api import read_pfm  # noqa: E402
+
+# name, xml (relative to REF/scenes), test film size (w, h), [(mode, spp)], committed?
+# One blob per scene (at the XML's own film size); tests override the film size when loading it.
+CASES = [
+    ("cbox", "cbox/cbox.xml", (128, 128), [("A", 1), ("B", 1), ("B", 64)], True),
+    ("veach_mi", "veach_mi/mi.xml", (192, 128), [("A", 1), ("B", 1), ("B", 64)], True),
+    ("sponza", "sponza/sponza.xml", (192, 144), [("A", 1), ("B", 1), ("B", 64)], False),
+    ("matpreview", "matpreview/matpreview.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+]
+
+
+def run(cmd):
+    r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
+    if r.returncode != 0:
+        print(r.stdout[-2000:])
+        raise SystemExit(f"command failed: {' '.join(cmd)}")
+    return r.stdout
+
+
+def main():
+    only = set(sys.argv[1:])
+    os.makedirs(os.path.join(ROOT, "scenes_flat"), exist_ok=True)
+    manifest_path = os.path.join(ROOT, "tests/golden/manifest.json")
+    manifest = json.load(open(manifest_path)) if os.path.exists(manifest_path) else {}
+    for name, xml, res, renders, committed in CASES:
+        if only and name not in only:
+            continue
+        outdir = os.path.join(ROOT, "tests/golden" if committed else "scenes_flat")
+        xml_path = os.path.join(REF, "scenes", xml)
+        blob = os.path.join(outdir, name + ".ljs")
+        res_args = ["--res", str(res[0]), str(res[1])]
+        print(run([FLATTEN, xml_path, blob]).strip().splitlines()[-1])
+        entry = {"xml": xml, "res": res, "committed": committed, "images": {}}
+        for mode, spp in renders:
+            pfm = f"/tmp/lj_golden_{name}_{mode}{spp}.pfm"
+            out = run([DRIVER, "render", xml_path, "-o", pfm, "--mode", mode, "--spp", str(spp)] + res_args)
+            stats = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+            img = read_pfm(pfm)
+            key = f"{mode}{spp}"
+            np.save(os.path.join(outdir, f"{name}_{key}.npy"), img)
+            entry["images"][key] = {"intersect_rays": stats["intersect_rays"], "occluded_rays": stats["occluded_rays"],
+                                    "mean": float(img.mean())}
+            os.remove(pfm)
+            print(f"  {name} {key}: mean {img.mean():.6f}, rays {stats['intersect_rays']}+{stats['occluded_rays']}")
+        manifest[name] = entry
+    json.dump(manifest, open(manifest_path, "w"), indent=1, sort_keys=True)
+
+
+if __name__ == "__main__":
+    main()
