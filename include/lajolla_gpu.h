@@ -207,6 +207,8 @@ const char *lj_last_error(void);
 int lj_scene_desc_save(const lj_scene_desc *desc, const char *path);
 int lj_scene_desc_load(const char *path, lj_scene_desc **out);    /* allocates; free with lj_scene_desc_free */
 void lj_scene_desc_free(lj_scene_desc *desc);
+/* page-lock (pin != 0) or unlock the arrays of a loaded desc so uploads run from pinned host memory */
+int lj_scene_desc_pin(lj_scene_desc *desc, int pin);
 
 #ifdef __cplusplus
 }

@@ -65,7 +65,7 @@ HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("geom_id", "<i4
 # every symbol include/lajolla_gpu.h declares
 ABI_SYMBOLS = ["lj_init", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", "lj_render", "lj_render_device",
                "lj_intersect_batch", "lj_scene_info", "lj_last_error", "lj_scene_desc_save", "lj_scene_desc_load",
-               "lj_scene_desc_free"]
+               "lj_scene_desc_free", "lj_scene_desc_pin"]
 
 _lib = None
 
@@ -95,6 +95,7 @@ def load_library():
     lib.lj_scene_desc_load.argtypes = [C.c_char_p, C.POINTER(C.c_void_p)]
     lib.lj_scene_desc_free.argtypes = [C.c_void_p]
     lib.lj_scene_desc_free.restype = None
+    lib.lj_scene_desc_pin.argtypes = [C.c_void_p, C.c_int]
     _lib = lib
     return lib
 
@@ -116,31 +117,54 @@ class LajollaGPU:
     def load_scene(self, blob_path, res=None, spp=None):
         return Scene(self, blob_path, res=res, spp=spp)
 
+    def scene_from_desc(self, desc):
+        return Scene(self, desc=desc)
+
     def close(self):
         if self.handle:
             self.lib.lj_shutdown(self.handle)
             self.handle = C.c_void_p()
 
 
+class HostSceneDesc:
+    """A flattened scene held in HOST memory (lj_scene_desc_load); optionally page-locked."""
+
+    def __init__(self, blob_path, pin=False, res=None, spp=None):
+        self.lib = load_library()
+        self.handle = C.c_void_p()
+        _check(self.lib, self.lib.lj_scene_desc_load(os.fsencode(blob_path), C.byref(self.handle)), "lj_scene_desc_load")
+        self.nbytes = os.path.getsize(blob_path)
+        if res is not None:   # film-size override (lj_camera.width/height follow the two 4x4 f64 matrices)
+            wh = (C.c_int32 * 2).from_address(self.handle.value + 256)
+            wh[0], wh[1] = int(res[0]), int(res[1])
+        if spp is not None:   # lj_options.samples_per_pixel
+            opt = (C.c_int32 * 6).from_address(self.handle.value + 280)
+            opt[1] = int(spp)
+        self.pinned = bool(pin) and self.lib.lj_scene_desc_pin(self.handle, 1) == 0
+
+    def close(self):
+        if self.handle:
+            if self.pinned:
+                self.lib.lj_scene_desc_pin(self.handle, 0)
+            self.lib.lj_scene_desc_free(self.handle)
+            self.handle = C.c_void_p()
+
+
 class Scene:
     """A flattened scene blob (.ljs, written by bin/lj_flatten or LJ_SAVE_SCENE) resident on the GPU."""
 
-    def __init__(self, gpu, blob_path, res=None, spp=None):
+    def __init__(self, gpu, blob_path=None, res=None, spp=None, desc=None):
         self.gpu = gpu
         lib = gpu.lib
-        desc = C.c_void_p()
-        _check(lib, lib.lj_scene_desc_load(os.fsencode(blob_path), C.byref(desc)), "lj_scene_desc_load")
-        if res is not None:   # film-size override (lj_camera.width/height follow the two 4x4 f64 matrices)
-            wh = (C.c_int32 * 2).from_address(desc.value + 256)
-            wh[0], wh[1] = int(res[0]), int(res[1])
-        if spp is not None:   # lj_options.samples_per_pixel
-            opt = (C.c_int32 * 6).from_address(desc.value + 256 + 16 + 8)
-            opt[1] = int(spp)
+        own = desc is None
+        if own:
+            desc = HostSceneDesc(blob_path, res=res, spp=spp)
         self.handle = C.c_void_p()
         try:
-            _check(lib, lib.lj_scene_create(gpu.handle, desc, C.byref(self.handle)), "lj_scene_create")
+            _check(lib, lib.lj_scene_create(gpu.handle, desc.handle, C.byref(self.handle)), "lj_scene_create")
         finally:
-            lib.lj_scene_desc_free(desc)
+            if own:
+                desc.close()
         w, h, spp = C.c_int32(), C.c_int32(), C.c_int32()
         self.build_stats = Stats()
         _check(lib, lib.lj_scene_info(self.handle, C.byref(w), C.byref(h), C.byref(spp), C.byref(self.build_stats)), "lj_scene_info")

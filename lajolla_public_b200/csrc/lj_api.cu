@@ -263,3 +263,20 @@ extern "C" int lj_intersect_batch(lj_scene *s, const lj_ray *rays, int64_t n, lj
     if (e != cudaSuccess) { lj_set_error("lj_intersect_batch: %s", cudaGetErrorString(e)); return LJ_ECUDA; }
     return LJ_OK;
 }
+
+// ---------------- pinned host scene arrays ----------------
+extern "C" int lj_scene_desc_pin(lj_scene_desc *d, int pin) {
+    if (!d) { lj_set_error("lj_scene_desc_pin: null desc"); return LJ_EINVAL; }
+    struct A { const void *p; size_t bytes; } arr[] = {
+        {d->positions, d->num_positions * 3 * sizeof(double)}, {d->normals, d->num_positions * 3 * sizeof(double)},
+        {d->uvs, d->num_positions * 2 * sizeof(double)}, {d->indices, d->num_indices * 3 * sizeof(int32_t)},
+        {d->texels, d->num_texels * sizeof(double)}, {d->tables, d->num_tables * sizeof(double)},
+        {d->grid_data, d->num_grid_data * sizeof(double)}};
+    int rc = LJ_OK;
+    for (auto &a : arr) {
+        if (!a.p || a.bytes < 4096) continue;
+        cudaError_t e = pin ? cudaHostRegister((void *)a.p, a.bytes, cudaHostRegisterDefault) : cudaHostUnregister((void *)a.p);
+        if (e != cudaSuccess) { cudaGetLastError(); lj_set_error("lj_scene_desc_pin: %s", cudaGetErrorString(e)); rc = LJ_ECUDA; }
+    }
+    return rc;
+}
