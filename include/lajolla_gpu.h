@@ -168,7 +168,7 @@ typedef struct lj_render_params {
     int32_t tile_rank, tile_world;      /* 16x16 tiles dealt round-robin: tile_id % world == rank; world 0 => all */
     int32_t max_depth_override;    /* -100 => scene options */
     int32_t paths_in_flight;       /* wavefront pool size, 0 => auto */
-    int32_t flags;                 /* bit0: count traversal steps (nodes / prims per ray) */
+    int32_t flags;                 /* bit0: count traversal steps (nodes / prims per ray); bit1: per-stage CUDA-event times */
 } lj_render_params;
 
 typedef struct lj_stats {
@@ -176,10 +176,12 @@ typedef struct lj_stats {
     double upload_ms, bvh_build_ms;
     uint64_t samples;
     uint64_t rays_primary, rays_extension, rays_shadow;
-    uint64_t nodes_visited, prims_tested;   /* only with flags bit0 */
+    uint64_t nodes_visited, prims_tested;   /* only with flags bit0: closest-hit rays */
     uint64_t kernel_launches;
     double extend_ms, shadow_ms, shade_ms, generate_ms;   /* per-stage CUDA-event sums (flags bit1) */
     uint64_t bvh_nodes, bvh_prims;
+    uint64_t shadow_nodes_visited, shadow_prims_tested;   /* flags bit0, any-hit rays */
+    uint64_t iterations;                  /* wavefront iterations */
 } lj_stats;
 
 typedef struct lj_ray { float org[3], tnear, dir[3], tfar; } lj_ray;           /* RTCRay subset, f32 seam */

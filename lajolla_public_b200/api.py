@@ -40,7 +40,8 @@ class Stats(C.Structure):
                 ("rays_shadow", C.c_uint64), ("nodes_visited", C.c_uint64), ("prims_tested", C.c_uint64),
                 ("kernel_launches", C.c_uint64), ("extend_ms", C.c_double), ("shadow_ms", C.c_double),
                 ("shade_ms", C.c_double), ("generate_ms", C.c_double), ("bvh_nodes", C.c_uint64),
-                ("bvh_prims", C.c_uint64)]
+                ("bvh_prims", C.c_uint64), ("shadow_nodes_visited", C.c_uint64), ("shadow_prims_tested", C.c_uint64),
+                ("iterations", C.c_uint64)]
 
     @property
     def rays(self):

@@ -125,7 +125,9 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
     d.tri_verts = s->bvh.tri_verts; d.spheres = d_spheres;
     d.bvh2 = s->bvh.bvh2; d.bvh2_root = s->bvh.bvh2_root;
     d.bvh8 = s->bvh.bvh8;
-    if (s->bvh.bvh8) d.tri_verts = s->bvh.tri_verts8 ? s->bvh.tri_verts8 : s->bvh.tri_verts;
+    // LJ_BVH=2 keeps the binary tree for traversal (validation of the 8-wide path against it)
+    if (const char *bv = getenv("LJ_BVH")) if (atoi(bv) == 2) d.bvh8 = nullptr;
+    if (d.bvh8) d.tri_verts = s->bvh.tri_verts8;
     float ms = 0;
     cudaEventElapsedTime(&ms, e0, e1); s->build_stats.upload_ms = ms;
     cudaEventElapsedTime(&ms, e1, e2); s->build_stats.bvh_build_ms = ms;

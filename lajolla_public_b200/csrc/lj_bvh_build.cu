@@ -9,6 +9,8 @@
 #include "lj_bvh_build.h"
 
 #include <cub/device/device_radix_sort.cuh>
+#include <cub/device/device_scan.cuh>
+#include <cstdlib>
 #include <cfloat>
 #include <cstdio>
 #include <vector>
@@ -179,7 +181,125 @@ __global__ void k_emit_prims(int n, int num_tris, const int *vals, const double 
     }
 }
 
+// ---------------- PLOC (parallel locally-ordered clustering, Meister & Bittner 2018) ----------------
+// Clusters start as the Morton-sorted primitives.  Each round every cluster looks at its
+// PLOC_R neighbours on either side (in the current order) for the partner with the smallest
+// merged surface area; mutually-nearest pairs are merged into a new inner node, the array is
+// compacted (order preserved), and the rounds repeat until one cluster is left.
+constexpr int PLOC_R = 24;
+constexpr int PLOC_B = 256;
+
+__device__ __forceinline__ float union_area(const float4 &alo, const float4 &ahi, const float4 &blo, const float4 &bhi) {
+    float dx = fmaxf(ahi.x, bhi.x) - fminf(alo.x, blo.x);
+    float dy = fmaxf(ahi.y, bhi.y) - fminf(alo.y, blo.y);
+    float dz = fmaxf(ahi.z, bhi.z) - fminf(alo.z, blo.z);
+    return dx * dy + dy * dz + dz * dx;
+}
+
+__global__ void k_ploc_init(int n, const int *vals, const float4 *prim_lo, const float4 *prim_hi,
+                            int *cid, int *ccount, float4 *clo, float4 *chi) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    int p = vals[i];
+    cid[i] = ~i; ccount[i] = 1; clo[i] = prim_lo[p]; chi[i] = prim_hi[p];
+}
+
+__global__ void __launch_bounds__(PLOC_B) k_ploc_nn(int m, const float4 *clo, const float4 *chi, int *nn) {
+    __shared__ float4 slo[PLOC_B + 2 * PLOC_R], shi[PLOC_B + 2 * PLOC_R];
+    int base = blockIdx.x * PLOC_B - PLOC_R;
+    for (int t = threadIdx.x; t < PLOC_B + 2 * PLOC_R; t += PLOC_B) {
+        int g = base + t;
+        if (g >= 0 && g < m) { slo[t] = clo[g]; shi[t] = chi[g]; }
+    }
+    __syncthreads();
+    int i = blockIdx.x * PLOC_B + threadIdx.x;
+    if (i >= m) return;
+    int li = threadIdx.x + PLOC_R;
+    float4 lo = slo[li], hi = shi[li];
+    float best = FLT_MAX; int bj = -1;
+    for (int o = -PLOC_R; o <= PLOC_R; o++) {
+        int j = i + o;
+        if (o == 0 || j < 0 || j >= m) continue;
+        float a = union_area(lo, hi, slo[li + o], shi[li + o]);
+        if (a < best) { best = a; bj = j; }     // ties keep the smaller j
+    }
+    nn[i] = bj;
+}
+
+__global__ void k_ploc_merge(int m, const int *nn, int *cid, int *ccount, float4 *clo, float4 *chi, int *valid,
+                             int *left, int *right, int *count, float4 *node_lo, float4 *node_hi, int *node_counter) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m) return;
+    int j = nn[i];
+    int v = 1;
+    if (j >= 0 && nn[j] == i) {
+        if (i < j) {
+            int id = atomicAdd(node_counter, 1);
+            float4 lo = clo[i], hi = chi[i], lo2 = clo[j], hi2 = chi[j];
+            lo = make_float4(fminf(lo.x, lo2.x), fminf(lo.y, lo2.y), fminf(lo.z, lo2.z), 0.f);
+            hi = make_float4(fmaxf(hi.x, hi2.x), fmaxf(hi.y, hi2.y), fmaxf(hi.z, hi2.z), 0.f);
+            left[id] = cid[i]; right[id] = cid[j];
+            int c = ccount[i] + ccount[j];
+            count[id] = c; node_lo[id] = lo; node_hi[id] = hi;
+            cid[i] = id; ccount[i] = c; clo[i] = lo; chi[i] = hi;
+        } else v = 0;
+    }
+    valid[i] = v;
+}
+
+__global__ void k_ploc_compact(int m, const int *valid, const int *pos, const int *cid, const int *ccount,
+                               const float4 *clo, const float4 *chi, int *cid2, int *ccount2, float4 *clo2, float4 *chi2) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= m || !valid[i]) return;
+    int p = pos[i];
+    cid2[p] = cid[i]; ccount2[p] = ccount[i]; clo2[p] = clo[i]; chi2[p] = chi[i];
+}
+
+// counts for the radix tree (LBVH path): size of the leaf range under each inner node
+__global__ void k_lbvh_counts(int n, const int *left, const int *right, int *count) {
+    int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n - 1) return;
+    int c = i; while (c >= 0) c = left[c];
+    int first = ~c;
+    c = i; while (c >= 0) c = right[c];
+    count[i] = ~c - first + 1;
+}
+
 } // namespace
+
+static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float4 *prim_hi,
+                      int *left, int *right, int *count, float4 *node_lo, float4 *node_hi, int *root_out, char *err) {
+    int *cid[2] = {nullptr, nullptr}, *cc[2] = {nullptr, nullptr}, *nn = nullptr, *valid = nullptr, *pos = nullptr, *counter = nullptr;
+    float4 *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
+    void *tmp = nullptr; size_t tmp_bytes = 0;
+    for (int b = 0; b < 2; b++) {
+        CK(cudaMalloc(&cid[b], 4 * (size_t)n)); CK(cudaMalloc(&cc[b], 4 * (size_t)n));
+        CK(cudaMalloc(&clo[b], sizeof(float4) * n)); CK(cudaMalloc(&chi[b], sizeof(float4) * n));
+    }
+    CK(cudaMalloc(&nn, 4 * (size_t)n)); CK(cudaMalloc(&valid, 4 * (size_t)(n + 1))); CK(cudaMalloc(&pos, 4 * (size_t)(n + 1)));
+    CK(cudaMalloc(&counter, 4)); CK(cudaMemset(counter, 0, 4));
+    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, valid, pos, n + 1));
+    CK(cudaMalloc(&tmp, tmp_bytes));
+    k_ploc_init<<<(n + 255) / 256, 256>>>(n, vals, prim_lo, prim_hi, cid[0], cc[0], clo[0], chi[0]);
+    int m = n, cur = 0, rounds = 0;
+    while (m > 1) {
+        int g = (m + PLOC_B - 1) / PLOC_B;
+        k_ploc_nn<<<g, PLOC_B>>>(m, clo[cur], chi[cur], nn);
+        k_ploc_merge<<<(m + 255) / 256, 256>>>(m, nn, cid[cur], cc[cur], clo[cur], chi[cur], valid, left, right, count, node_lo, node_hi, counter);
+        CK(cudaMemsetAsync(valid + m, 0, 4));
+        CK(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, valid, pos, m + 1));
+        k_ploc_compact<<<(m + 255) / 256, 256>>>(m, valid, pos, cid[cur], cc[cur], clo[cur], chi[cur], cid[1 - cur], cc[1 - cur], clo[1 - cur], chi[1 - cur]);
+        int m_new = 0;
+        CK(cudaMemcpy(&m_new, pos + m, 4, cudaMemcpyDeviceToHost));
+        if (m_new >= m || m_new < 1) { snprintf(err, 256, "PLOC made no progress (%d -> %d clusters)", m, m_new); return -1; }
+        m = m_new; cur = 1 - cur;
+        if (++rounds > 4096) { snprintf(err, 256, "PLOC did not converge"); return -1; }
+    }
+    CK(cudaMemcpy(root_out, cid[cur], 4, cudaMemcpyDeviceToHost));
+    for (int b = 0; b < 2; b++) { cudaFree(cid[b]); cudaFree(cc[b]); cudaFree(clo[b]); cudaFree(chi[b]); }
+    cudaFree(nn); cudaFree(valid); cudaFree(pos); cudaFree(counter); cudaFree(tmp);
+    return 0;
+}
 
 int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
     const int n = in.num_tris + in.num_spheres;
@@ -191,7 +311,7 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
     float4 *prim_lo = nullptr, *prim_hi = nullptr, *node_lo = nullptr, *node_hi = nullptr;
     float *bounds = nullptr;
     unsigned long long *keys = nullptr, *keys2 = nullptr;
-    int *vals = nullptr, *vals2 = nullptr, *left = nullptr, *right = nullptr, *par_i = nullptr, *par_l = nullptr, *flags = nullptr;
+    int *vals = nullptr, *vals2 = nullptr, *left = nullptr, *right = nullptr, *par_i = nullptr, *par_l = nullptr, *flags = nullptr, *count = nullptr;
     void *tmp = nullptr;
     CK(cudaMalloc(&prim_lo, sizeof(float4) * n)); CK(cudaMalloc(&prim_hi, sizeof(float4) * n));
     CK(cudaMalloc(&bounds, sizeof(float) * 6));
@@ -220,21 +340,28 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
         CK(cudaMalloc(&par_i, 4 * (size_t)n)); CK(cudaMalloc(&par_l, 4 * (size_t)n));
         CK(cudaMalloc(&flags, 4 * (size_t)n)); CK(cudaMemset(flags, 0, 4 * (size_t)n));
         CK(cudaMalloc(&node_lo, sizeof(float4) * n)); CK(cudaMalloc(&node_hi, sizeof(float4) * n));
-        k_radix_tree<<<G, B>>>(n, keys2, left, right, par_i, par_l);
-        CK(cudaGetLastError());
-        k_fit<<<G, B>>>(n, vals2, prim_lo, prim_hi, left, right, par_i, par_l, flags, node_lo, node_hi);
-        CK(cudaGetLastError());
+        CK(cudaMalloc(&count, 4 * (size_t)n));
+        const char *bsel = getenv("LJ_BUILDER");       // "lbvh" keeps the plain radix tree; default PLOC
+        if (bsel && bsel[0] == 'l') {
+            k_radix_tree<<<G, B>>>(n, keys2, left, right, par_i, par_l);
+            CK(cudaGetLastError());
+            k_fit<<<G, B>>>(n, vals2, prim_lo, prim_hi, left, right, par_i, par_l, flags, node_lo, node_hi);
+            CK(cudaGetLastError());
+            k_lbvh_counts<<<G, B>>>(n, left, right, count);
+            out.bvh2_root = 0;
+        } else {
+            if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, &out.bvh2_root, err) != 0) return -1;
+        }
         CK(cudaMalloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
         k_emit_bvh2<<<G, B>>>(n, left, right, node_lo, node_hi, out.bvh2);
         CK(cudaGetLastError());
-        out.bvh2_root = 0;
         out.num_bvh2 = n - 1;
     }
     CK(cudaDeviceSynchronize());
     // the 8-wide collapse consumes the binary tree (lj_bvh8_build.cu)
-    int rc = lj_bvh8_collapse(n, out.bvh2, out.tri_verts, left, right, node_lo, node_hi, vals2, prim_lo, prim_hi, out, err);
+    int rc = lj_bvh8_collapse(n, out.bvh2_root, out.tri_verts, left, right, count, node_lo, node_hi, vals2, prim_lo, prim_hi, out, err);
     cudaFree(prim_lo); cudaFree(prim_hi); cudaFree(bounds); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(left); cudaFree(right); cudaFree(par_i); cudaFree(par_l); cudaFree(flags); cudaFree(node_lo); cudaFree(node_hi); cudaFree(tmp);
+    cudaFree(left); cudaFree(right); cudaFree(par_i); cudaFree(par_l); cudaFree(flags); cudaFree(node_lo); cudaFree(node_hi); cudaFree(tmp); cudaFree(count);
     return rc;
 }
 

@@ -25,6 +25,6 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err /* >= 2
 void lj_bvh_free(BvhBuildOutput &out);
 
 // 8-wide collapse + quantisation of the binary tree (device arrays of the builder)
-int lj_bvh8_collapse(int n, const Bvh2Node *bvh2, const float4 *tri_verts, const int *left, const int *right,
+int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left, const int *right, const int *count,
                      const float4 *node_lo, const float4 *node_hi, const int *sorted_prim,
                      const float4 *prim_lo, const float4 *prim_hi, BvhBuildOutput &out, char *err);

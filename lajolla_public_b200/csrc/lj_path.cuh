@@ -21,11 +21,6 @@ LJ_D bool scene_occluded(const DScene &sc, const Ray &ray) {
     return trace_any(sc, rf);
 }
 
-LJ_D Ray make_ray(d3 org, d3 dir, double tnear, double tfar) { Ray r; r.org = org; r.dir = dir; r.tnear = tnear; r.tfar = tfar; return r; }
-
-// The NEE half of one bounce (path_tracing.h:96-207): returns C1 * w1 and the shadow ray to test.
-// `valid` is false when the contribution is zero regardless of visibility.
-struct NeeResult { d3 contrib; Ray shadow_ray; bool need_shadow; };
 
 LJ_D d3 path_tracing_sample(const DScene &sc, int x, int y, Pcg32 &rng, RayCounters &rc) {
     const int w = sc.camera.width, h = sc.camera.height;

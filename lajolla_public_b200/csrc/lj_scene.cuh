@@ -69,6 +69,7 @@ struct PointAndNormal { d3 position, normal; };                  // point_and_no
 // What crosses the ray-cast seam back (RTCRay.tfar + RTCHit, all f32 / u32)
 struct Hit { float t, u, v; int geom, prim; float ngx, ngy, ngz; };
 
+LJ_D Ray make_ray(d3 org, d3 dir, double tnear, double tfar) { Ray r; r.org = org; r.dir = dir; r.tnear = tnear; r.tfar = tfar; return r; }
 LJ_D RayDiff init_ray_differential(int w, int h) { RayDiff r; r.radius = 0; r.spread = 0.25 / (w > h ? w : h); return r; }
 LJ_D double rd_transfer(const RayDiff &r, double dist) { return r.radius + r.spread * dist; }
 LJ_D double rd_reflect(const RayDiff &r, double mean_curvature, double roughness) {

@@ -1,6 +1,169 @@
-// Entry points of the ray-cast seam used by the integrators.
+// Traversal of the compressed 8-wide BVH (Bvh8Node, 80 bytes = five 16-byte loads per
+// node) with a short stack of (child group base, pending-hit mask) pairs; children are
+// visited in octant order, so no distance sort is needed.  The traversal is written as a
+// resumable state machine (Trav8: init / step / finish) so the wavefront trace kernels can
+// keep warps full by handing a finished lane a new ray (lj_wavefront.cu), while the
+// whole-path engines simply run it to completion (trace_closest / trace_any below, the
+// rtcIntersect1 / rtcOccluded1 of this build).
+// Primitive tests and the closest-hit rule are those of lj_traverse.cuh; the running best
+// hit is kept as (t, leaf slot) only and the full record (u, v, Ng) is recomputed once at
+// the end with the same arithmetic.
 #pragma once
 #include "lj_traverse.cuh"
 
-LJ_D bool trace_closest(const DScene &sc, const RayF &r, Hit *h) { return traverse_bvh2<false>(sc, r, h); }
-LJ_D bool trace_any(const DScene &sc, const RayF &r) { return traverse_bvh2<true>(sc, r, nullptr); }
+#ifndef LJ_BVH8_STACK
+#define LJ_BVH8_STACK 24
+#endif
+
+LJ_D unsigned byte_of(unsigned w, int i) { return (w >> (8 * i)) & 0xffu; }
+
+struct Trav8 {
+    RayF r;
+    float idx, idy, idz;
+    unsigned oct_inv;
+    float best_t; int best_slot;
+    uint2 ng; int sp;
+    uint2 stack[LJ_BVH8_STACK];
+    unsigned n_nodes, n_prims;
+
+    LJ_D void init(const RayF &ray) {
+        r = ray;
+        // inverse direction with zero components replaced by a huge finite value of the right sign
+        const float sx = fabsf(r.dx) > 1e-20f ? r.dx : copysignf(1e-20f, r.dx);
+        const float sy = fabsf(r.dy) > 1e-20f ? r.dy : copysignf(1e-20f, r.dy);
+        const float sz = fabsf(r.dz) > 1e-20f ? r.dz : copysignf(1e-20f, r.dz);
+        idx = 1.0f / sx; idy = 1.0f / sy; idz = 1.0f / sz;
+        oct_inv = (sx >= 0.f ? 1u : 0u) | (sy >= 0.f ? 2u : 0u) | (sz >= 0.f ? 4u : 0u);
+        best_t = r.tfar; best_slot = -1;
+        ng = make_uint2(0u, 0x80000000u);      // root: one pending inner child, empty imask
+        sp = 0; n_nodes = 0; n_prims = 0;
+    }
+
+    // closest-hit rule on ties: smaller (geomID, primID) wins
+    LJ_D bool tie_less(const DScene &sc, int slot_a, int slot_b) const {
+        int ga = __float_as_int(__ldg(&sc.tri_verts[3 * slot_a]).w), gb = __float_as_int(__ldg(&sc.tri_verts[3 * slot_b]).w);
+        if (ga != gb) return ga < gb;
+        return __float_as_int(__ldg(&sc.tri_verts[3 * slot_a + 1]).w) < __float_as_int(__ldg(&sc.tri_verts[3 * slot_b + 1]).w);
+    }
+
+    // test one primitive slot; returns true if it is an accepted hit (ANY: stop)
+    template <bool ANY>
+    LJ_D bool prim(const DScene &sc, int slot) {
+        const float4 a = __ldg(&sc.tri_verts[3 * slot + 0]);
+        const float4 b = __ldg(&sc.tri_verts[3 * slot + 1]);
+        const float4 c = __ldg(&sc.tri_verts[3 * slot + 2]);
+        float t;
+        if (__float_as_int(c.w) == 0) {
+            TriHit h;
+            const f3 O{r.ox, r.oy, r.oz}, D{r.dx, r.dy, r.dz};
+            if (!tri_test(O, D, r.tnear, r.tfar, f3{a.x, a.y, a.z}, f3{b.x, b.y, b.z}, f3{c.x, c.y, c.z}, h)) return false;
+            t = h.t;
+        } else {
+            double ts = sphere_test(r, sc.spheres[__float_as_int(a.x)], r.tfar);
+            if (ts < 0) return false;
+            t = (float)ts;
+        }
+        if (ANY) return true;
+        if (best_slot < 0 || t < best_t || (t == best_t && tie_less(sc, slot, best_slot))) { best_t = t; best_slot = slot; }
+        return false;
+    }
+
+    // one traversal step: open one pending inner child (if any), test its children, then test the
+    // primitives of the leaf children that were hit.  Returns false when the traversal is over
+    // (ANY: `found` tells whether an occluder was met).
+    template <bool ANY, bool COUNT>
+    LJ_D bool step(const DScene &sc, bool &found) {
+        uint2 tg = make_uint2(0u, 0u);
+        if (ng.y & 0xff000000u) {
+            const int bit = 31 - __clz(ng.y);
+            ng.y &= ~(1u << bit);
+            if ((ng.y & 0xff000000u) && sp < LJ_BVH8_STACK) stack[sp++] = ng;
+            const unsigned slot = (unsigned)(bit - 24) ^ oct_inv;
+            const unsigned rel = __popc(ng.y & 0xffu & ((1u << slot) - 1u));
+            const float4 *np = reinterpret_cast<const float4 *>(&sc.bvh8[ng.x + rel]);
+            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+            if (COUNT) n_nodes++;
+            const unsigned ew = __float_as_uint(n0.w);
+            const float adx = __uint_as_float(byte_of(ew, 0) << 23) * idx;
+            const float ady = __uint_as_float(byte_of(ew, 1) << 23) * idy;
+            const float adz = __uint_as_float(byte_of(ew, 2) << 23) * idz;
+            const float bx = (n0.x - r.ox) * idx, by = (n0.y - r.oy) * idy, bz = (n0.z - r.oz) * idz;
+            unsigned hitmask = 0;
+#pragma unroll
+            for (int half = 0; half < 2; half++) {
+                const unsigned meta4 = __float_as_uint(half ? n1.w : n1.z);
+                const unsigned qlx = __float_as_uint(half ? n2.y : n2.x), qly = __float_as_uint(half ? n2.w : n2.z);
+                const unsigned qlz = __float_as_uint(half ? n3.y : n3.x), qhx = __float_as_uint(half ? n3.w : n3.z);
+                const unsigned qhy = __float_as_uint(half ? n4.y : n4.x), qhz = __float_as_uint(half ? n4.w : n4.z);
+                // near / far plane bytes per axis depend on the direction sign
+                const unsigned nx = idx < 0.f ? qhx : qlx, fx = idx < 0.f ? qlx : qhx;
+                const unsigned ny = idy < 0.f ? qhy : qly, fy = idy < 0.f ? qly : qhy;
+                const unsigned nz = idz < 0.f ? qhz : qlz, fz = idz < 0.f ? qlz : qhz;
+#pragma unroll
+                for (int j = 0; j < 4; j++) {
+                    const unsigned m = byte_of(meta4, j);
+                    const float t0x = fmaf((float)byte_of(nx, j), adx, bx), t1x = fmaf((float)byte_of(fx, j), adx, bx);
+                    const float t0y = fmaf((float)byte_of(ny, j), ady, by), t1y = fmaf((float)byte_of(fy, j), ady, by);
+                    const float t0z = fmaf((float)byte_of(nz, j), adz, bz), t1z = fmaf((float)byte_of(fz, j), adz, bz);
+                    const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
+                    const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, best_t));
+                    // padded comparison (the planes are computed with a few roundings)
+                    if (m != 0 && t0 - fabsf(t0) * 2e-6f <= t1 + fabsf(t1) * 2e-6f) {
+                        unsigned shift = m & 31u;
+                        if ((m & 0x18u) == 0x18u) shift ^= oct_inv;      // inner child: slot -> traversal priority
+                        hitmask |= (m >> 5) << shift;
+                    }
+                }
+            }
+            ng = make_uint2(__float_as_uint(n1.x), (hitmask & 0xff000000u) | (ew >> 24));
+            tg = make_uint2(__float_as_uint(n1.y), hitmask & 0x00ffffffu);
+        }
+        while (tg.y) {
+            const int b = __ffs(tg.y) - 1;
+            tg.y &= tg.y - 1;
+            if (COUNT) n_prims++;
+            if (prim<ANY>(sc, (int)tg.x + b)) { found = true; return false; }
+        }
+        if (!(ng.y & 0xff000000u)) {
+            if (sp == 0) return false;
+            ng = stack[--sp];
+        }
+        return true;
+    }
+
+    // full hit record of the winning primitive (same arithmetic as during traversal)
+    LJ_D bool finish(const DScene &sc, Hit *h) const {
+        if (best_slot < 0) return false;
+        const float4 a = __ldg(&sc.tri_verts[3 * best_slot + 0]);
+        const float4 b = __ldg(&sc.tri_verts[3 * best_slot + 1]);
+        const float4 c = __ldg(&sc.tri_verts[3 * best_slot + 2]);
+        h->geom = __float_as_int(a.w); h->prim = __float_as_int(b.w);
+        if (__float_as_int(c.w) == 0) {
+            TriHit th;
+            const f3 O{r.ox, r.oy, r.oz}, D{r.dx, r.dy, r.dz};
+            tri_test(O, D, r.tnear, r.tfar, f3{a.x, a.y, a.z}, f3{b.x, b.y, b.z}, f3{c.x, c.y, c.z}, th);
+            h->t = th.t; h->u = th.u; h->v = th.v; h->ngx = th.ng.x; h->ngy = th.ng.y; h->ngz = th.ng.z;
+        } else {
+            const SpherePrim s = sc.spheres[__float_as_int(a.x)];
+            double ts = sphere_test(r, s, r.tfar);
+            h->t = (float)ts;
+            sphere_hit_details(r, s, ts, *h);
+        }
+        return true;
+    }
+};
+
+LJ_D bool trace_closest(const DScene &sc, const RayF &r, Hit *h) {
+    if (!sc.bvh8) return traverse_bvh2<false>(sc, r, h);
+    Trav8 tv; tv.init(r);
+    bool found = false;
+    while (tv.step<false, false>(sc, found)) {}
+    return tv.finish(sc, h);
+}
+LJ_D bool trace_any(const DScene &sc, const RayF &r) {
+    if (!sc.bvh8) return traverse_bvh2<true>(sc, r, nullptr);
+    Trav8 tv; tv.init(r);
+    bool found = false;
+    while (tv.step<true, false>(sc, found)) {}
+    return found;
+}

@@ -1,4 +1,538 @@
+// Wavefront path tracer (mode B streams): path_tracing.h:7-325 split into stages
+//   generate -> extend (closest hit) -> shade[material kind] / miss -> shadow (any hit) -> accumulate
+// connected by queues compacted with warp-aggregated atomics.  A pool of path
+// slots is kept full by regeneration: slot (pixel, k) renders samples
+// s_begin+k, s_begin+k+K, ... of its pixel one after the other and owns its own
+// accumulator, so no atomics touch radiance and the per-pixel sum order is fixed.
+//
+// Per-slot state lives in HBM as 32/64-byte records (gathered by slot id after
+// compaction, so records are whole 32-byte sectors); queues and shadow / extend
+// ray records are written and read by queue position (coalesced).
 #include "lj_internal.h"
+#include "lj_materials.cuh"
+#include "lj_traverse8.cuh"
+#include <cstdio>
+#include <cstdlib>
+
+namespace {
+
+enum { Q_EXT = 0, Q_SHADOW = 1, Q_REGEN = 2, Q_FINISH = 3, Q_MISS = 4, Q_KIND0 = 5, Q_COUNT = Q_KIND0 + LJ_MAT_KIND_COUNT };
+
+struct __align__(16) RayRec { double ox, oy, oz, spread, dx, dy, dz, eta_scale; };          // 64 B
+struct __align__(16) ThrRec { double tx, ty, tz, p2, fx, fy, fz; int nv, sample; };          // 64 B
+struct __align__(16) RadRec { double rx, ry, rz; unsigned long long rng; };                  // 32 B
+struct __align__(16) HitRec { float t, u, v; int geom, prim; float ngx, ngy, ngz; };         // 32 B
+struct __align__(16) ExtRec { RayF ray; };                                                   // 32 B
+struct __align__(16) ShadowRec { RayF ray; double cx, cy, cz; int slot, _pad; };             // 64 B
+
+struct WfPool {
+    int capacity, K;
+    long long npix;
+    RayRec *ray; ThrRec *thr; RadRec *rad; HitRec *hit;
+    double *accum;              // 3 per slot
+    ExtRec *ext_ray; int *ext_slot;
+    ShadowRec *shadow;
+    int *q_regen, *q_miss, *q_finish, *q_kind[LJ_MAT_KIND_COUNT];
+    int *counts;                // Q_COUNT live queue sizes
+};
+
+// Warp-aggregated queue push: lanes of the calling (possibly partial) warp that push to the
+// same queue elect one leader, which reserves a contiguous range with a single atomicAdd.
+LJ_D int queue_push_pos(int *counter) {
+    unsigned mask = __activemask();
+    unsigned peers = __match_any_sync(mask, (unsigned long long)counter);
+    int leader = __ffs(peers) - 1;
+    int lane = threadIdx.x & 31;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(peers));
+    base = __shfl_sync(peers, base, leader);
+    return base + __popc(peers & ((1u << lane) - 1));
+}
+
+LJ_D void terminate_path(const WfPool &wp, int slot, d3 radiance) {
+    double *a = wp.accum + 3 * (size_t)slot;
+    a[0] += radiance.x; a[1] += radiance.y; a[2] += radiance.z;      // render.cpp:92: radiance += path_tracing(...)
+    wp.q_regen[queue_push_pos(&wp.counts[Q_REGEN])] = slot;
+}
+
+LJ_D void push_extend(const WfPool &wp, int slot, const Ray &r) {
+    int pos = queue_push_pos(&wp.counts[Q_EXT]);
+    ExtRec e; e.ray = to_rayf(r);
+    wp.ext_ray[pos] = e;
+    wp.ext_slot[pos] = slot;
+}
+
+// ---- stage: generate (path_tracing.h:9-14, render.cpp:88-93 loop head) ----
+__global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n_regen, int s_end, int ntx, int tile_rank, int tile_world) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_regen; i += gridDim.x * blockDim.x) {
+        int slot = wp.q_regen[i];
+        ThrRec tr = wp.thr[slot];
+        int s = tr.sample + wp.K;
+        int pix = (int)(slot % wp.npix);
+        int w = sc.camera.width, h = sc.camera.height;
+        int x = pix % w, y = pix / w;
+        bool mine = true;
+        if (tile_world > 0) mine = (((y / 16) * ntx + (x / 16)) % tile_world) == tile_rank;
+        if (s >= s_end || !mine) continue;                      // slot exhausted
+        Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)wp.npix + (unsigned long long)pix);
+        double u_first = pcg_real(rng), u_second = pcg_real(rng);   // right-to-left argument evaluation, see lj_path.cuh
+        Ray ray = sample_primary(sc.camera, mk2((x + u_second) / w, (y + u_first) / h));
+        RayDiff rd = init_ray_differential(w, h);
+        RayRec rr; rr.ox = ray.org.x; rr.oy = ray.org.y; rr.oz = ray.org.z; rr.spread = rd.spread;
+        rr.dx = ray.dir.x; rr.dy = ray.dir.y; rr.dz = ray.dir.z; rr.eta_scale = 1;
+        tr.tx = tr.ty = tr.tz = 1; tr.p2 = 0; tr.fx = tr.fy = tr.fz = 0; tr.nv = 2; tr.sample = s;
+        RadRec ra; ra.rx = ra.ry = ra.rz = 0; ra.rng = rng.state;
+        wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
+        push_extend(wp, slot, ray);
+    }
+}
+
+// ---- persistent trace kernels ----
+// Rays differ a lot in traversal length, so a warp that just walks its 32 rays to the end runs
+// mostly empty.  Instead every warp pulls rays from the queue through one atomic work counter
+// and, whenever fewer than REFILL_BELOW lanes are still traversing, hands the idle lanes new
+// rays (warp-aggregated fetch) before stepping on.
+constexpr int REFILL_BELOW = 22;
+enum { W_EXT = 24, W_SHADOW = 25 };     // work counters inside wp.counts
+
+template <bool ANY>
+LJ_D bool warp_fetch(int *work_counter, int n, int &ray_idx, bool &exhausted) {
+    // called by all 32 lanes; lanes with ray_idx < 0 ask for work
+    const unsigned idle = __ballot_sync(0xffffffffu, ray_idx < 0);
+    if (!idle || exhausted) return false;
+    const int lane = threadIdx.x & 31;
+    const int n_idle = __popc(idle);
+    const int leader = __ffs(idle) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(work_counter, n_idle);
+    base = __shfl_sync(0xffffffffu, base, leader);
+    if (base + n_idle >= n) exhausted = true;
+    if (ray_idx < 0) {
+        int i = base + __popc(idle & ((1u << lane) - 1u));
+        if (i < n) { ray_idx = i; return true; }
+    }
+    return false;
+}
+
+// ---- stage: extend = rtcIntersect1 (intersection.cpp:32) + classification by material kind ----
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters) {
+    const int n = min(n_upper, wp.counts[Q_EXT]);
+    int ray_idx = -1; bool exhausted = false;
+    Trav8 tv;
+    unsigned nn = 0, np = 0;
+    while (true) {
+        if (warp_fetch<false>(&wp.counts[W_EXT], n, ray_idx, exhausted)) tv.init(wp.ext_ray[ray_idx].ray);
+        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
+        const int stop_below = exhausted ? 1 : REFILL_BELOW;
+        while (true) {
+            if (ray_idx >= 0) {
+                bool found = false;
+                if (!tv.step<false, COUNT>(sc, found)) {
+                    const int slot = wp.ext_slot[ray_idx];
+                    Hit h; HitRec hr; int q;
+                    if (tv.finish(sc, &h)) {
+                        hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
+                        q = Q_KIND0 + sc.materials[sc.shapes[h.geom].material_id].kind;
+                    } else {
+                        hr.t = 0; hr.u = hr.v = 0; hr.geom = -1; hr.prim = -1; hr.ngx = hr.ngy = hr.ngz = 0;
+                        q = Q_MISS;
+                    }
+                    wp.hit[slot] = hr;
+                    int *queue = (q == Q_MISS) ? wp.q_miss : wp.q_kind[q - Q_KIND0];
+                    queue[queue_push_pos(&wp.counts[q])] = slot;
+                    if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
+                    ray_idx = -1;
+                }
+            }
+            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0)) < stop_below) break;
+        }
+    }
+    if (COUNT) { atomicAdd(&trav_counters[0], (unsigned long long)nn); atomicAdd(&trav_counters[1], (unsigned long long)np); }
+}
+
+// ---- stage: shadow = rtcOccluded1 (intersection.cpp:83) + accumulate the NEE term ----
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_wf_shadow(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters) {
+    const int n = min(n_upper, wp.counts[Q_SHADOW]);
+    int ray_idx = -1; bool exhausted = false;
+    Trav8 tv;
+    unsigned nn = 0, np = 0;
+    while (true) {
+        if (warp_fetch<true>(&wp.counts[W_SHADOW], n, ray_idx, exhausted)) tv.init(wp.shadow[ray_idx].ray);
+        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
+        const int stop_below = exhausted ? 1 : REFILL_BELOW;
+        while (true) {
+            if (ray_idx >= 0) {
+                bool found = false;
+                if (!tv.step<true, COUNT>(sc, found)) {
+                    if (!found) {
+                        const ShadowRec *s = &wp.shadow[ray_idx];
+                        RadRec *ra = &wp.rad[s->slot];
+                        ra->rx += s->cx; ra->ry += s->cy; ra->rz += s->cz;        // path_tracing.h:207
+                    }
+                    if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
+                    ray_idx = -1;
+                }
+            }
+            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0)) < stop_below) break;
+        }
+    }
+    if (COUNT) { atomicAdd(&trav_counters[2], (unsigned long long)nn); atomicAdd(&trav_counters[3], (unsigned long long)np); }
+}
+
+// ---- stage: finish = accumulate paths whose last NEE term had to wait for the shadow stage ----
+__global__ void __launch_bounds__(128) k_wf_finish(WfPool wp, int n_upper) {
+    int n = min(n_upper, wp.counts[Q_FINISH]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int slot = wp.q_finish[i];
+        RadRec ra = wp.rad[slot];
+        terminate_path(wp, slot, mk3(ra.rx, ra.ry, ra.rz));
+    }
+}
+
+__global__ void k_wf_reset(int *counts, int a, int b, int c) {
+    if (threadIdx.x == 0) { if (a >= 0) counts[a] = 0; if (b >= 0) counts[b] = 0; if (c >= 0) counts[c] = 0; }
+}
+__global__ void k_wf_reset_kinds(int *counts) {
+    if (threadIdx.x < Q_COUNT - Q_FINISH) counts[Q_FINISH + threadIdx.x] = 0;
+    if (threadIdx.x == 0) { counts[24] = 0; counts[25] = 0; }
+}
+
+__global__ void k_wf_init(WfPool wp, int s_begin) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < wp.capacity; i += (long long)gridDim.x * blockDim.x) {
+        int k = (int)(i / wp.npix);
+        ThrRec tr; tr.tx = tr.ty = tr.tz = 0; tr.p2 = 0; tr.fx = tr.fy = tr.fz = 0; tr.nv = 0;
+        tr.sample = s_begin + k - wp.K;
+        wp.thr[i] = tr;
+        wp.accum[3 * i] = 0; wp.accum[3 * i + 1] = 0; wp.accum[3 * i + 2] = 0;
+        wp.q_regen[i] = (int)i;
+    }
+}
+
+__global__ void k_wf_sum(long long npix, int K, const double *accum, double *sum) {
+    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix * 3) return;
+    double a = 0;
+    for (int k = 0; k < K; k++) a += accum[(size_t)k * npix * 3 + i];
+    sum[i] = a;
+}
+
+} // namespace
+
+namespace {
+
+// One bounce of path_tracing.h's loop body (:96-232) at a fresh vertex: NEE (shadow record),
+// BSDF sampling (next extension ray + the f / p2 the next stage needs).  Returns false when the
+// path ends here.  KIND is the compile-time material kind of the queue being processed.
+template <int KIND>
+LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const PathVertex &vertex, d3 dir_view,
+                           Pcg32 &rng, d3 throughput, RayRec &rr, ThrRec &tr, bool &pushed_shadow) {
+    MatParams mat = load_mat_params(sc, vertex);
+    mat.kind = KIND;
+    const double eps = sc.eps;
+    d2 light_uv; light_uv.x = pcg_real(rng); light_uv.y = pcg_real(rng);
+    double light_w = pcg_real(rng);
+    double shape_w = pcg_real(rng);
+    int light_id = sample_table1d(sc.light_cdf, sc.num_lights, light_w);
+    const lj_light &light = sc.lights[light_id];
+    PointAndNormal pl = sample_point_on_light(sc, light, vertex.position, light_uv, shape_w);
+    {
+        // G as if unoccluded; the shadow stage zeroes the term when the ray is blocked
+        double G; d3 dir_light; double tfar;
+        if (light.kind != LJ_LIGHT_ENVMAP) {
+            dir_light = normalize(pl.position - vertex.position);
+            tfar = (1 - eps) * distance(pl.position, vertex.position);
+            G = lmax(-dot(dir_light, pl.normal), 0.0) / distance_squared(pl.position, vertex.position);
+        } else {
+            dir_light = -pl.normal; tfar = INFINITY; G = 1;
+        }
+        double p1 = __ldg(sc.light_pmf + light_id) * pdf_point_on_light(sc, light, pl, vertex.position);
+        if (G > 0 && p1 > 0) {
+            d3 f = bsdf_eval(mat, vertex, dir_view, dir_light);
+            d3 L = light_emission(sc, light, -dir_light, 0.0, pl);
+            d3 C1 = G * f * L;
+            double p2 = bsdf_pdf(mat, vertex, dir_view, dir_light);
+            p2 *= G;
+            double w1 = (p1 * p1) / (p1 * p1 + p2 * p2);
+            C1 = C1 / p1;
+            d3 contrib = throughput * C1 * w1;
+            if (contrib.x != 0 || contrib.y != 0 || contrib.z != 0) {
+                ShadowRec s;
+                s.ray = to_rayf(make_ray(vertex.position, dir_light, eps, tfar));
+                s.cx = contrib.x; s.cy = contrib.y; s.cz = contrib.z; s.slot = slot; s._pad = 0;
+                wp.shadow[queue_push_pos(&wp.counts[Q_SHADOW])] = s;
+                pushed_shadow = true;
+            }
+        }
+    }
+    d2 bsdf_uv; bsdf_uv.x = pcg_real(rng); bsdf_uv.y = pcg_real(rng);
+    double bsdf_w = pcg_real(rng);
+    BSDFSample bs;
+    if (!bsdf_sample(mat, vertex, dir_view, bsdf_uv, bsdf_w, bs)) return false;
+    RayDiff rd; rd.radius = 0; rd.spread = rr.spread;
+    if (bs.eta == 0) {
+        rr.spread = rd_reflect(rd, vertex.mean_curvature, bs.roughness);
+    } else {
+        rr.spread = rd_refract(rd, vertex.mean_curvature, bs.eta, bs.roughness);
+        rr.eta_scale /= (bs.eta * bs.eta);
+    }
+    d3 f = bsdf_eval(mat, vertex, dir_view, bs.dir_out);
+    double p2 = bsdf_pdf(mat, vertex, dir_view, bs.dir_out);
+    if (p2 <= 0) return false;                     // path_tracing.h:253-256 (the reference traces the ray first and discards it)
+    rr.ox = vertex.position.x; rr.oy = vertex.position.y; rr.oz = vertex.position.z;
+    rr.dx = bs.dir_out.x; rr.dy = bs.dir_out.y; rr.dz = bs.dir_out.z;
+    tr.fx = f.x; tr.fy = f.y; tr.fz = f.z; tr.p2 = p2;
+    return true;
+}
+
+// ---- stage: shade, one launch per material kind present in the scene ----
+template <int KIND>
+__global__ void __launch_bounds__(128) k_wf_shade(DScene sc, WfPool wp, int n_upper) {
+    int n = min(n_upper, wp.counts[Q_KIND0 + KIND]);
+    const int *queue = wp.q_kind[KIND];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int slot = queue[i];
+        RayRec rr = wp.ray[slot];
+        ThrRec tr = wp.thr[slot];
+        RadRec ra = wp.rad[slot];
+        HitRec hr = wp.hit[slot];
+        int pix = (int)(slot % wp.npix);
+        Pcg32 rng; rng.state = ra.rng;
+        rng.inc = (((unsigned long long)tr.sample * (unsigned long long)wp.npix + (unsigned long long)pix) << 1u) | 1u;
+        Ray ray = make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), 0, 0);
+        d3 throughput = mk3(tr.tx, tr.ty, tr.tz), radiance = mk3(ra.rx, ra.ry, ra.rz);
+        Hit h; h.t = hr.t; h.u = hr.u; h.v = hr.v; h.geom = hr.geom; h.prim = hr.prim; h.ngx = hr.ngx; h.ngy = hr.ngy; h.ngz = hr.ngz;
+        bool primary = tr.nv == 2;
+        RayDiff rd; rd.radius = 0; rd.spread = primary ? rr.spread : 0.0;   // bounce rays: intersect(scene, bsdf_ray) default differential
+        PathVertex vertex = make_vertex(sc, ray, h, rd);
+        bool alive = true;
+        bool is_light = sc.shapes[vertex.shape_id].area_light_id >= 0;
+        if (primary) {
+            if (is_light) radiance += throughput * vertex_emission(sc, vertex, -ray.dir);   // path_tracing.h:58-61
+            tr.nv = 3;
+        } else {
+            // finish the previous bounce with the new vertex (path_tracing.h:242-322)
+            d3 f = mk3(tr.fx, tr.fy, tr.fz);
+            double G = fabs(dot(ray.dir, vertex.geometry_normal)) / distance_squared(vertex.position, ray.org);
+            double p2 = tr.p2 * G;
+            if (is_light) {
+                d3 L = vertex_emission(sc, vertex, -ray.dir);
+                d3 C2 = G * f * L;
+                int lid = sc.shapes[vertex.shape_id].area_light_id;
+                PointAndNormal lp; lp.position = vertex.position; lp.normal = vertex.geometry_normal;
+                double p1 = __ldg(sc.light_pmf + lid) * pdf_point_on_light(sc, sc.lights[lid], lp, ray.org);
+                double w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
+                C2 = C2 / p2;
+                radiance += throughput * C2 * w2;
+            }
+            double rr_prob = 1;
+            if (tr.nv - 1 >= sc.options.rr_depth) {
+                rr_prob = lmin(max3((1 / rr.eta_scale) * throughput), 0.95);
+                if (pcg_real(rng) > rr_prob) alive = false;
+            }
+            if (alive) {
+                throughput = throughput * (G * f) / (p2 * rr_prob);
+                tr.nv += 1;
+            }
+        }
+        const int max_depth = sc.options.max_depth;
+        if (alive && !(max_depth == -1 || tr.nv <= max_depth + 1)) alive = false;
+        bool pushed_shadow = false;
+        if (alive) alive = bounce_at_vertex<KIND>(sc, wp, slot, vertex, -ray.dir, rng, throughput, rr, tr, pushed_shadow);
+        if (!alive) {
+            if (!pushed_shadow) { terminate_path(wp, slot, radiance); continue; }
+            // the path ends here but its last NEE term is still in the shadow queue: park the
+            // radiance and let the finish stage (after the shadow stage) do the accumulation
+            ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
+            wp.rad[slot] = ra;
+            wp.q_finish[queue_push_pos(&wp.counts[Q_FINISH])] = slot;
+            continue;
+        }
+        tr.tx = throughput.x; tr.ty = throughput.y; tr.tz = throughput.z;
+        ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
+        wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
+        push_extend(wp, slot, make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), sc.eps, INFINITY));
+    }
+}
+
+// ---- stage: miss (path_tracing.h:17-28 and :283-307) ----
+__global__ void __launch_bounds__(128) k_wf_miss(DScene sc, WfPool wp, int n_upper) {
+    int n = min(n_upper, wp.counts[Q_MISS]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int slot = wp.q_miss[i];
+        RayRec rr = wp.ray[slot];
+        ThrRec tr = wp.thr[slot];
+        RadRec ra = wp.rad[slot];
+        d3 radiance = mk3(ra.rx, ra.ry, ra.rz);
+        if (sc.envmap_light_id != -1) {
+            const lj_light &env = sc.lights[sc.envmap_light_id];
+            d3 dir = mk3(rr.dx, rr.dy, rr.dz);
+            PointAndNormal dummy; dummy.position = mk3(0.0); dummy.normal = mk3(0.0);
+            d3 L = light_emission(sc, env, -dir, rr.spread, dummy);
+            if (tr.nv == 2) {
+                radiance = L;
+            } else {
+                d3 throughput = mk3(tr.tx, tr.ty, tr.tz), f = mk3(tr.fx, tr.fy, tr.fz);
+                double G = 1;
+                double p2 = tr.p2 * G;
+                d3 C2 = G * f * L;
+                PointAndNormal lp; lp.position = mk3(0.0); lp.normal = -dir;
+                double p1 = __ldg(sc.light_pmf + sc.envmap_light_id) * pdf_point_on_light(sc, env, lp, mk3(rr.ox, rr.oy, rr.oz));
+                double w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
+                C2 = C2 / p2;
+                radiance += throughput * C2 * w2;
+            }
+        }
+        terminate_path(wp, slot, radiance);
+    }
+}
+
+template <int KIND>
+void launch_shade(const DScene &d, const WfPool &wp, int n_upper, int grid_cap) {
+    int grid = (n_upper + 127) / 128;
+    if (grid > grid_cap) grid = grid_cap;
+    k_wf_shade<KIND><<<grid, 128>>>(d, wp, n_upper);
+}
+
+} // namespace
+
+static int ensure_pool(lj_scene *s, int capacity, int K, long long npix, WfPool &wp) {
+    size_t cap = (size_t)capacity;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    size_t o_ray = take(cap * sizeof(RayRec)), o_thr = take(cap * sizeof(ThrRec)), o_rad = take(cap * sizeof(RadRec));
+    size_t o_hit = take(cap * sizeof(HitRec)), o_acc = take(cap * 3 * sizeof(double));
+    size_t o_er = take(cap * sizeof(ExtRec)), o_es = take(cap * sizeof(int)), o_sh = take(cap * sizeof(ShadowRec));
+    size_t o_qr = take(cap * sizeof(int)), o_qm = take(cap * sizeof(int)), o_qf = take(cap * sizeof(int));
+    size_t o_qk[LJ_MAT_KIND_COUNT];
+    for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) o_qk[k] = take(cap * sizeof(int));
+    size_t o_cnt = take(64 * sizeof(int));
+    if (off > s->wf_pool_bytes) {
+        if (s->wf_pool) cudaFree(s->wf_pool);
+        s->wf_pool = nullptr; s->wf_pool_bytes = 0;
+        LJ_CUDA(cudaMalloc(&s->wf_pool, off));
+        s->wf_pool_bytes = off;
+    }
+    char *b = (char *)s->wf_pool;
+    wp.capacity = capacity; wp.K = K; wp.npix = npix;
+    wp.ray = (RayRec *)(b + o_ray); wp.thr = (ThrRec *)(b + o_thr); wp.rad = (RadRec *)(b + o_rad); wp.hit = (HitRec *)(b + o_hit);
+    wp.accum = (double *)(b + o_acc); wp.ext_ray = (ExtRec *)(b + o_er); wp.ext_slot = (int *)(b + o_es);
+    wp.shadow = (ShadowRec *)(b + o_sh); wp.q_regen = (int *)(b + o_qr); wp.q_miss = (int *)(b + o_qm); wp.q_finish = (int *)(b + o_qf);
+    for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) wp.q_kind[k] = (int *)(b + o_qk[k]);
+    wp.counts = (int *)(b + o_cnt);
+    return LJ_OK;
+}
+
 int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st) {
-    return lj_render_megakernel(s, rl, dev_sum, st);
+    const DScene &d = s->d;
+    if (!d.bvh8) return lj_render_megakernel(s, rl, dev_sum, st);   // LJ_BVH=2 validation mode: binary tree only
+    const long long npix = (long long)rl.width * rl.height;
+    const int nsamp = rl.s_end - rl.s_begin;
+    // pool sizing: K slots per pixel, ~2M paths in flight unless the caller says otherwise
+    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (2LL << 20);
+    int K = (int)((target + npix - 1) / npix);
+    if (K > nsamp) K = nsamp;
+    if (K < 1) K = 1;
+    if (npix * K > 0x7fffffffLL / 4) { lj_set_error("wavefront: pool too large"); return LJ_EINVAL; }
+    const int capacity = (int)(npix * K);
+    WfPool wp;
+    int rc = ensure_pool(s, capacity, K, npix, wp);
+    if (rc) return rc;
+
+    // which material kinds exist in this scene (host copy of the kinds, once per render)
+    bool kind_present[LJ_MAT_KIND_COUNT] = {false};
+    {
+        std::vector<lj_material> mats(d.num_materials);
+        if (d.num_materials) LJ_CUDA(cudaMemcpy(mats.data(), d.materials, sizeof(lj_material) * d.num_materials, cudaMemcpyDeviceToHost));
+        for (const lj_material &m : mats) if (m.kind >= 0 && m.kind < LJ_MAT_KIND_COUNT) kind_present[m.kind] = true;
+    }
+    const int sm = s->ctx->sm_count;
+    const int trace_grid_cap = sm * 16, shade_grid_cap = sm * 16;
+    const bool trace_iters = getenv("LJ_WF_TRACE") != nullptr;
+    const bool stage_timing = (rl.p.flags & 2) != 0 || trace_iters;
+    const bool counting = (rl.p.flags & 1) != 0 && d.bvh8 != nullptr;
+    unsigned long long *trav = (unsigned long long *)(wp.counts + 32);   // 4 x u64 after the queue counters
+    cudaEvent_t ev[5];
+    if (stage_timing) for (auto &e : ev) cudaEventCreate(&e);
+
+    LJ_CUDA(cudaMemsetAsync(wp.counts, 0, 64 * sizeof(int)));
+    k_wf_init<<<sm * 8, 256>>>(wp, rl.s_begin);
+    LJ_CUDA(cudaGetLastError());
+    int n_regen = capacity, n_ext = 0;
+    unsigned long long launches = 2, rays_primary = 0, rays_ext = 0, rays_shadow = 0;
+    int h_counts[Q_COUNT];
+    auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
+    while (n_regen > 0 || n_ext > 0) {
+        if (stage_timing) cudaEventRecord(ev[0]);
+        if (n_regen > 0) {
+            k_wf_generate<<<grid_for(n_regen, shade_grid_cap), 128>>>(d, wp, n_regen, rl.s_end, rl.ntx, rl.p.tile_rank, rl.p.tile_world);
+            launches++;
+        }
+        k_wf_reset<<<1, 32>>>(wp.counts, Q_REGEN, -1, -1);
+        if (stage_timing) cudaEventRecord(ev[1]);
+        int ext_upper = n_ext + n_regen;
+        if (counting) k_wf_extend<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
+        else k_wf_extend<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
+        k_wf_reset<<<1, 32>>>(wp.counts, Q_EXT, -1, -1);
+        if (stage_timing) cudaEventRecord(ev[2]);
+        if (kind_present[0]) launch_shade<0>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[1]) launch_shade<1>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[2]) launch_shade<2>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[3]) launch_shade<3>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[4]) launch_shade<4>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[5]) launch_shade<5>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[6]) launch_shade<6>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[7]) launch_shade<7>(d, wp, ext_upper, shade_grid_cap);
+        if (kind_present[8]) launch_shade<8>(d, wp, ext_upper, shade_grid_cap);
+        k_wf_miss<<<grid_for(ext_upper, shade_grid_cap), 128>>>(d, wp, ext_upper);
+        if (stage_timing) cudaEventRecord(ev[3]);
+        if (counting) k_wf_shadow<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
+        else k_wf_shadow<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
+        k_wf_finish<<<grid_for(ext_upper, shade_grid_cap), 128>>>(wp, ext_upper);
+        if (stage_timing) cudaEventRecord(ev[4]);
+        // one readback per iteration: queue sizes for the next one (also the ray counts)
+        LJ_CUDA(cudaMemcpy(h_counts, wp.counts, sizeof h_counts, cudaMemcpyDeviceToHost));
+        k_wf_reset_kinds<<<1, 32>>>(wp.counts);
+        k_wf_reset<<<1, 32>>>(wp.counts, Q_SHADOW, -1, -1);
+        launches += 8;
+        for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
+        int traced = h_counts[Q_MISS];
+        for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) traced += h_counts[Q_KIND0 + k];
+        // rays traced this iteration = hits + misses; the first n_regen-derived ones are primaries
+        int prim_now = traced - n_ext;
+        rays_primary += prim_now > 0 ? prim_now : 0;
+        rays_ext += traced - (prim_now > 0 ? prim_now : 0);
+        rays_shadow += h_counts[Q_SHADOW];
+        if (stage_timing) {
+            float ms;
+            cudaEventElapsedTime(&ms, ev[0], ev[1]); st->generate_ms += ms;
+            cudaEventElapsedTime(&ms, ev[1], ev[2]); st->extend_ms += ms;
+            cudaEventElapsedTime(&ms, ev[2], ev[3]); st->shade_ms += ms;
+            cudaEventElapsedTime(&ms, ev[3], ev[4]); st->shadow_ms += ms;
+        }
+        if (trace_iters) {
+            float ms_e = 0, ms_s = 0, ms_h = 0;
+            if (stage_timing) { cudaEventElapsedTime(&ms_e, ev[1], ev[2]); cudaEventElapsedTime(&ms_s, ev[2], ev[3]); cudaEventElapsedTime(&ms_h, ev[3], ev[4]); }
+            fprintf(stderr, "[wf] iter %llu: traced %d (regen %d) shadow %d -> next ext %d regen %d | extend %.3f shade %.3f shadow %.3f ms\n",
+                    (unsigned long long)st->iterations, traced, n_regen, h_counts[Q_SHADOW], h_counts[Q_EXT], h_counts[Q_REGEN], ms_e, ms_s, ms_h);
+        }
+        n_regen = h_counts[Q_REGEN];
+        n_ext = h_counts[Q_EXT];
+        st->iterations++;
+    }
+    k_wf_sum<<<(unsigned)((npix * 3 + 255) / 256), 256>>>(npix, K, wp.accum, dev_sum);
+    LJ_CUDA(cudaGetLastError());
+    if (counting) {
+        unsigned long long h_trav[4];
+        LJ_CUDA(cudaMemcpy(h_trav, trav, sizeof h_trav, cudaMemcpyDeviceToHost));
+        st->nodes_visited = h_trav[0]; st->prims_tested = h_trav[1];          // closest-hit rays
+        st->shadow_nodes_visited = h_trav[2]; st->shadow_prims_tested = h_trav[3];
+    }
+    launches++;
+    if (stage_timing) for (auto &e : ev) cudaEventDestroy(e);
+    st->kernel_launches += launches;
+    st->rays_primary += rays_primary; st->rays_extension += rays_ext; st->rays_shadow += rays_shadow;
+    st->samples = (uint64_t)npix * (uint64_t)nsamp;
+    return LJ_OK;
 }
