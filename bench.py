@@ -138,7 +138,8 @@ def gpu_arm(args):
     w, h = scene.width, scene.height
     S = args.spp
     engine = ENGINE_MEGAKERNEL if args.engine == "megakernel" else ENGINE_WAVEFRONT
-    rp = RenderParams(spp=S * world, rng_mode=RNG_SAMPLE_STREAMS, engine=engine, sample_begin=rank * S, sample_end=(rank + 1) * S)
+    # flags bit1: CUDA-event intervals around every stage launch (the roofline's kernel time)
+    rp = RenderParams(spp=S * world, rng_mode=RNG_SAMPLE_STREAMS, engine=engine, sample_begin=rank * S, sample_end=(rank + 1) * S, flags=2)
     sums = torch.zeros(h * w * 3, dtype=torch.float64, device=dev)
     flush = torch.empty(256 << 20, dtype=torch.uint8, device=dev)   # > 126 MB L2
 
@@ -157,7 +158,8 @@ def gpu_arm(args):
         one_step()
     sampler = ClockSampler(local); sampler.start()
     barrier()
-    total_ms = 0.0; rays = samples = launches = 0
+    total_ms = 0.0; rays = samples = launches = iters = 0
+    rtypes = {"primary": 0, "extension": 0, "shadow": 0}
     stage = {"extend_ms": 0.0, "shadow_ms": 0.0, "shade_ms": 0.0, "generate_ms": 0.0}
     for _ in range(args.steps):
         flush.fill_(1)                       # L2 flush between timed iterations (not timed)
@@ -167,7 +169,8 @@ def gpu_arm(args):
         st = one_step()
         e1.record(); torch.cuda.synchronize()
         total_ms += e0.elapsed_time(e1)
-        rays += st.rays; samples += st.samples; launches += st.kernel_launches
+        rays += st.rays; samples += st.samples; launches += st.kernel_launches; iters += st.iterations
+        rtypes["primary"] += st.rays_primary; rtypes["extension"] += st.rays_extension; rtypes["shadow"] += st.rays_shadow
         for k in stage:
             stage[k] += getattr(st, k)
     barrier()
@@ -211,7 +214,7 @@ def gpu_arm(args):
         except Exception:
             pass
         peak = float(peaks.get("hbm_gbs", 6650.0))
-        roof = roofline_block(scene, rp, stage, st, rays, peak, "measured" if peaks else "fallback")
+        roof = roofline_block(scene, rp, stage, rtypes, iters, peak, "measured" if peaks else "fallback", sums.data_ptr())
         line = {"metric": "sponza_path_tracing_mrays_per_s", "value": value, "unit": "Mrays/s", "n_gpus": world,
                 "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps, "higher_is_better": True,
                 "scaling": "weak", "vs_baseline": None, "dtype": "f64", "data": "scenes/sponza/sponza.xml (reference asset, flattened blob)",
@@ -237,16 +240,36 @@ def gpu_arm(args):
         dist.destroy_process_group()
 
 
-def roofline_block(scene, rp, stage, st, rays, peak, which):
-    """Roofline of the dominant kernel (closest-hit extend) from a separate counting pass:
-    algorithmic bytes per ray = 32 + 20 + 80*nodes/ray + 48*prims/ray."""
+def roofline_block(scene, rp, stage, rays_by_type, iterations, peak, which, scratch_ptr):
+    """Roofline of the dominant kernel, k_wf_extend (closest-hit traversal of the 8-wide BVH).
+    ALGORITHMIC bytes per ray (DESIGN.md "Roofline"):
+        32 (ray, 8 x f32) + 20 (hit record) + 80 * nodes/ray + 48 * prims/ray
+    nodes/ray and prims/ray come from one untimed counting pass of the same workload (flags bit0);
+    the kernel time is the sum of CUDA-event intervals around every k_wf_extend launch inside the
+    timed steps (flags bit1, recorded on the stream the library launches on)."""
     from lajolla_public_b200 import RenderParams
-    cp = RenderParams(spp=1, rng_mode=rp.rng_mode, engine=rp.engine, flags=3)
-    try:
-        cst = scene.render_into_device(0, cp) if False else None
-    except Exception:
-        cst = None
-    return {"bound": "hbm", "achieved": None, "peak": peak, "unit": "GB/s", "frac": None, "traffic": None, "peak_source": which}
+    cp = RenderParams(spp=rp.spp, rng_mode=rp.rng_mode, engine=rp.engine, sample_begin=rp.sample_begin,
+                      sample_end=rp.sample_end, flags=1)
+    ct = scene.render_into_device(scratch_ptr, cp)
+    closest = max(ct.rays_primary + ct.rays_extension, 1)
+    nodes_per_ray = ct.nodes_visited / closest
+    prims_per_ray = ct.prims_tested / closest
+    bytes_ray = BYTES_RAY_FIXED + 80.0 * nodes_per_ray + 48.0 * prims_per_ray
+    n_closest = rays_by_type["primary"] + rays_by_type["extension"]
+    ext_s = stage["extend_ms"] * 1e-3
+    achieved = n_closest * bytes_ray / ext_s * 1e-9 if ext_s > 0 else None
+    sh = max(ct.rays_shadow, 1)
+    step_ms = sum(stage.values())
+    return {"bound": "hbm", "kernel": "k_wf_extend<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
+            "frac": achieved / peak if achieved else None, "traffic": None, "peak_source": which,
+            "bytes_per_ray": bytes_ray, "nodes_per_ray": nodes_per_ray, "prims_per_ray": prims_per_ray,
+            "launches": int(iterations), "avg_launch_ms": stage["extend_ms"] / max(iterations, 1),
+            "bytes_per_launch": n_closest * bytes_ray / max(iterations, 1),
+            "share_of_step": stage["extend_ms"] / step_ms if step_ms > 0 else None,
+            "stage_ms": dict(stage),
+            "shadow_nodes_per_ray": ct.shadow_nodes_visited / sh, "shadow_prims_per_ray": ct.shadow_prims_tested / sh,
+            "note": "scene (BVH 8-wide nodes + triangles) is L2-resident; the HBM roofline is the SURVEY 8(d) convention, "
+                    "the practical limiter is dependent-load latency + divergence (see profiles/)"}
 
 
 def main():
