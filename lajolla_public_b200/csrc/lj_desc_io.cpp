@@ -34,7 +34,11 @@ extern "C" int lj_scene_desc_save(const lj_scene_desc *d, const char *path) {
     FILE *f = fopen(path, "wb");
     if (!f) { lj_set_error("lj_scene_desc_save: cannot open %s", path); return LJ_EIO; }
     Arr a[NARR]; arrays_of(d, a);
-    bool ok = fwrite("LJS1", 1, 4, f) == 4 && fwrite(d, sizeof *d, 1, f) == 1;
+    lj_scene_desc hdr = *d;      // host pointers mean nothing in a file: store them as null so blobs are reproducible
+    hdr.shapes = nullptr; hdr.lights = nullptr; hdr.materials = nullptr; hdr.media = nullptr; hdr.textures = nullptr;
+    hdr.images1 = nullptr; hdr.images3 = nullptr; hdr.positions = nullptr; hdr.normals = nullptr; hdr.uvs = nullptr;
+    hdr.indices = nullptr; hdr.texels = nullptr; hdr.tables = nullptr; hdr.grid_data = nullptr;
+    bool ok = fwrite("LJS1", 1, 4, f) == 4 && fwrite(&hdr, sizeof hdr, 1, f) == 1;
     for (int i = 0; ok && i < NARR; i++) {
         ok = fwrite(&a[i].bytes, 8, 1, f) == 1 && (a[i].bytes == 0 || fwrite(a[i].ptr, 1, a[i].bytes, f) == a[i].bytes);
     }
