@@ -260,8 +260,13 @@ def roofline_block(scene, rp, stage, rays_by_type, iterations, peak, which, scra
     achieved = n_closest * bytes_ray / ext_s * 1e-9 if ext_s > 0 else None
     sh = max(ct.rays_shadow, 1)
     step_ms = sum(stage.values())
+    traffic = None
+    try:   # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel (profiles/)
+        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_wf_extend<0>"]["dram_bytes_per_launch"]
+    except Exception:
+        pass
     return {"bound": "hbm", "kernel": "k_wf_extend<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak if achieved else None, "traffic": None, "peak_source": which,
+            "frac": achieved / peak if achieved else None, "traffic": traffic, "peak_source": which,
             "bytes_per_ray": bytes_ray, "nodes_per_ray": nodes_per_ray, "prims_per_ray": prims_per_ray,
             "launches": int(iterations), "avg_launch_ms": stage["extend_ms"] / max(iterations, 1),
             "bytes_per_launch": n_closest * bytes_ray / max(iterations, 1),
