@@ -27,6 +27,19 @@ CASES = [
     ("veach_mi", "veach_mi/mi.xml", (192, 128), [("A", 1), ("B", 1), ("B", 64)], True),
     ("sponza", "sponza/sponza.xml", (192, 144), [("A", 1), ("B", 1), ("B", 64)], False),
     ("matpreview", "matpreview/matpreview.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    # vol_path_tracing.h: versions 1, 2 and the final integrator (3..6), homogeneous + heterogeneous media
+    ("volpath_test1", "volpath_test/volpath_test1.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("volpath_test2", "volpath_test/volpath_test2.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("volpath_test3", "volpath_test/volpath_test3.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("volpath_test4", "volpath_test/volpath_test4.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("volpath_test4_2", "volpath_test/volpath_test4_2.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("volpath_test5", "volpath_test/volpath_test5.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("volpath_test5_2", "volpath_test/volpath_test5_2.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("volpath_test6", "volpath_test/volpath_test6.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("vol_cbox", "volpath_test/vol_cbox.xml", (96, 96), [("A", 1), ("B", 1), ("B", 16)], True),
+    ("vol_cbox_teapot", "volpath_test/vol_cbox_teapot.xml", (96, 96), [("A", 1), ("B", 1), ("B", 16)], False),
+    ("hetvol", "volpath_test/hetvol.xml", (96, 72), [("A", 1), ("B", 1), ("B", 16)], False),
+    ("hetvol_colored", "volpath_test/hetvol_colored.xml", (96, 72), [("A", 1), ("B", 1), ("B", 16)], False),
 ]
 
 
