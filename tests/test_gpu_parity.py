@@ -41,10 +41,13 @@ def load_case(gpu, manifest, name):
 
 
 # stated 1-spp pixel-match bars per scene (mode A = reference tile streams, mode B = per-sample streams)
-BARS = {"cbox": 0.99, "veach_mi": 0.99, "sponza": 0.99, "matpreview": 0.95}
+BARS = {"cbox": 0.99, "veach_mi": 0.99, "sponza": 0.99, "matpreview": 0.95, "simple_sphere": 0.99, "pixel_filter_test": 0.99,
+        "disney_diffuse": 0.95, "disney_metal": 0.95, "disney_glass": 0.95, "disney_clearcoat": 0.95, "disney_sheen": 0.95,
+        "disney_bsdf": 0.95}
+PATH_SCENES = list(BARS)
 
 
-@pytest.mark.parametrize("name", ["cbox", "veach_mi", "sponza", "matpreview"])
+@pytest.mark.parametrize("name", PATH_SCENES)
 @pytest.mark.parametrize("mode", ["A", "B"])
 def test_one_spp_path_match(gpu, manifest, name, mode):
     from lajolla_public_b200 import RenderParams, RNG_TILE_STREAMS, RNG_SAMPLE_STREAMS, ENGINE_MEGAKERNEL
@@ -62,7 +65,7 @@ def test_one_spp_path_match(gpu, manifest, name, mode):
     assert frac >= BARS[name]
 
 
-@pytest.mark.parametrize("name", ["cbox", "veach_mi", "sponza", "matpreview"])
+@pytest.mark.parametrize("name", PATH_SCENES)
 @pytest.mark.parametrize("engine", ["megakernel", "wavefront"])
 def test_many_spp_same_streams(gpu, manifest, name, engine):
     """64 spp on identical per-sample streams: images must agree far below the noise level."""

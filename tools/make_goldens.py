@@ -27,6 +27,15 @@ CASES = [
     ("veach_mi", "veach_mi/mi.xml", (192, 128), [("A", 1), ("B", 1), ("B", 64)], True),
     ("sponza", "sponza/sponza.xml", (192, 144), [("A", 1), ("B", 1), ("B", 64)], False),
     ("matpreview", "matpreview/matpreview.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    # scenes/disney_bsdf_test: the matpreview geometry with each Disney lobe / the full Disney BSDF
+    ("disney_diffuse", "disney_bsdf_test/disney_diffuse.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    ("disney_metal", "disney_bsdf_test/disney_metal.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    ("disney_glass", "disney_bsdf_test/disney_glass.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    ("disney_clearcoat", "disney_bsdf_test/disney_clearcoat.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    ("disney_sheen", "disney_bsdf_test/disney_sheen.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    ("disney_bsdf", "disney_bsdf_test/disney_bsdf.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
+    ("simple_sphere", "disney_bsdf_test/simple_sphere.xml", (128, 128), [("A", 1), ("B", 1), ("B", 64)], True),
+    ("pixel_filter_test", "pixel_filter_test/pixel_filter_test.xml", (128, 128), [("A", 1), ("B", 1), ("B", 64)], True),
     # vol_path_tracing.h: versions 1, 2 and the final integrator (3..6), homogeneous + heterogeneous media
     ("volpath_test1", "volpath_test/volpath_test1.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
     ("volpath_test2", "volpath_test/volpath_test2.xml", (64, 64), [("A", 1), ("B", 1), ("B", 16)], True),
