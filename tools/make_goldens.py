@@ -23,7 +23,7 @@ from lajolla_public_b200.api import read_pfm  # noqa: E402
 # name, xml (relative to REF/scenes), test film size (w, h), [(mode, spp)], committed?
 # One blob per scene (at the XML's own film size); tests override the film size when loading it.
 CASES = [
-    ("cbox", "cbox/cbox.xml", (128, 128), [("A", 1), ("B", 1), ("B", 64)], True),
+    ("cbox", "cbox/cbox.xml", (128, 128), [("A", 1), ("B", 1), ("B", 64), ("A", 1024), ("B", 1024)], True),
     ("veach_mi", "veach_mi/mi.xml", (192, 128), [("A", 1), ("B", 1), ("B", 64)], True),
     ("sponza", "sponza/sponza.xml", (192, 144), [("A", 1), ("B", 1), ("B", 64)], False),
     ("matpreview", "matpreview/matpreview.xml", (171, 128), [("A", 1), ("B", 1), ("B", 64)], False),
