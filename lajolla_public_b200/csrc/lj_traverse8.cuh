@@ -1,10 +1,15 @@
 // Traversal of the compressed 8-wide BVH (Bvh8Node, 80 bytes = five 16-byte loads per
 // node) with a short stack of (child group base, pending-hit mask) pairs; children are
 // visited in octant order, so no distance sort is needed.  The traversal is written as a
-// resumable state machine (Trav8: init / step / finish) so the wavefront trace kernels can
-// keep warps full by handing a finished lane a new ray (lj_wavefront.cu), while the
-// whole-path engines simply run it to completion (trace_closest / trace_any below, the
-// rtcIntersect1 / rtcOccluded1 of this build).
+// resumable state machine with two kinds of step -- node_step (open one inner child, slab-test
+// its 8 children) and prim_step (test one pending primitive) -- so the wavefront trace kernels
+// (lj_wavefront.cu) can (a) hand a finished lane a new ray and (b) let the warp VOTE on which
+// phase to run next, postponing primitive tests until enough lanes have one pending: the two
+// phases then run with mostly full warps instead of serialising behind each other.  The
+// whole-path engines simply run a ray to completion (trace_closest / trace_any below, the
+// rtcIntersect1 / rtcOccluded1 of this build).  Postponing changes only the ORDER of primitive
+// tests; the closest hit is the lexicographic minimum of (t, geomID, primID) and therefore
+// independent of that order.
 // Primitive tests and the closest-hit rule are those of lj_traverse.cuh; the running best
 // hit is kept as (t, leaf slot) only and the full record (u, v, Ng) is recomputed once at
 // the end with the same arithmetic.
@@ -12,18 +17,26 @@
 #include "lj_traverse.cuh"
 
 #ifndef LJ_BVH8_STACK
-#define LJ_BVH8_STACK 24
+#define LJ_BVH8_STACK 32
 #endif
 
 LJ_D unsigned byte_of(unsigned w, int i) { return (w >> (8 * i)) & 0xffu; }
+
+// exact u8 -> f32 without the (quarter-rate) conversion pipe: splice byte j of w into the mantissa
+// of 2^23 with one PRMT, then subtract 2^23 (exact)
+LJ_D float byte_to_float(unsigned w, int j) {
+    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + (unsigned)j)) - 8388608.0f;
+}
 
 struct Trav8 {
     RayF r;
     float idx, idy, idz;
     unsigned oct_inv;
     float best_t; int best_slot;
-    uint2 ng; int sp;
-    uint2 stack[LJ_BVH8_STACK];
+    uint2 ng;        // node group: x = child base, y = (pending inner-child hits << 24) | imask
+    uint2 tg;        // primitive group waiting to be tested: x = first slot, y = 24-bit pending mask
+    int sp;
+    uint2 stack[LJ_BVH8_STACK];   // node groups (y & 0xff000000 != 0) and postponed primitive groups (top byte 0)
     unsigned n_nodes, n_prims;
 
     LJ_D void init(const RayF &ray) {
@@ -36,8 +49,13 @@ struct Trav8 {
         oct_inv = (sx >= 0.f ? 1u : 0u) | (sy >= 0.f ? 2u : 0u) | (sz >= 0.f ? 4u : 0u);
         best_t = r.tfar; best_slot = -1;
         ng = make_uint2(0u, 0x80000000u);      // root: one pending inner child, empty imask
+        tg = make_uint2(0u, 0u);
         sp = 0; n_nodes = 0; n_prims = 0;
     }
+
+    LJ_D bool wants_node() const { return (ng.y & 0xff000000u) != 0u; }
+    LJ_D bool wants_prim() const { return tg.y != 0u; }
+    LJ_D bool active() const { return wants_node() || wants_prim(); }
 
     // closest-hit rule on ties: smaller (geomID, primID) wins
     LJ_D bool tie_less(const DScene &sc, int slot_a, int slot_b) const {
@@ -68,67 +86,103 @@ struct Trav8 {
         return false;
     }
 
-    // one traversal step: open one pending inner child (if any), test its children, then test the
-    // primitives of the leaf children that were hit.  Returns false when the traversal is over
-    // (ANY: `found` tells whether an occluder was met).
+    // After a phase: if the node group is exhausted, pull work from the stack.  Node groups go to
+    // `ng`; postponed primitive groups go to `tg` if it is free, otherwise the lane stays blocked
+    // on its primitive work (wants_node() false, wants_prim() true).
+    LJ_D void refill_from_stack() {
+        while (!wants_node() && sp > 0) {
+            const uint2 e = stack[sp - 1];
+            if (e.y & 0xff000000u) { ng = e; sp--; }
+            else if (tg.y == 0u) { tg = e; sp--; }
+            else break;
+        }
+    }
+
+    // Node phase: open one pending inner child and slab-test its 8 children.  Inner hits become
+    // the new node group; leaf hits become a primitive group, held in `tg` or postponed on the stack.
+    // Requires wants_node().  Returns true only if an occluder was found (ANY, stack-overflow path).
     template <bool ANY, bool COUNT>
-    LJ_D bool step(const DScene &sc, bool &found) {
-        uint2 tg = make_uint2(0u, 0u);
-        if (ng.y & 0xff000000u) {
-            const int bit = 31 - __clz(ng.y);
-            ng.y &= ~(1u << bit);
-            if ((ng.y & 0xff000000u) && sp < LJ_BVH8_STACK) stack[sp++] = ng;
-            const unsigned slot = (unsigned)(bit - 24) ^ oct_inv;
-            const unsigned rel = __popc(ng.y & 0xffu & ((1u << slot) - 1u));
-            const float4 *np = reinterpret_cast<const float4 *>(&sc.bvh8[ng.x + rel]);
-            const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
-            if (COUNT) n_nodes++;
-            const unsigned ew = __float_as_uint(n0.w);
-            const float adx = __uint_as_float(byte_of(ew, 0) << 23) * idx;
-            const float ady = __uint_as_float(byte_of(ew, 1) << 23) * idy;
-            const float adz = __uint_as_float(byte_of(ew, 2) << 23) * idz;
-            const float bx = (n0.x - r.ox) * idx, by = (n0.y - r.oy) * idy, bz = (n0.z - r.oz) * idz;
-            unsigned hitmask = 0;
+    LJ_D bool node_step(const DScene &sc) {
+        const int bit = 31 - __clz(ng.y);
+        ng.y &= ~(1u << bit);
+        if ((ng.y & 0xff000000u) && sp < LJ_BVH8_STACK) stack[sp++] = ng;
+        const unsigned slot = (unsigned)(bit - 24) ^ oct_inv;
+        const unsigned rel = __popc(ng.y & 0xffu & ((1u << slot) - 1u));
+        const float4 *np = reinterpret_cast<const float4 *>(&sc.bvh8[ng.x + rel]);
+        const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
+        if (COUNT) n_nodes++;
+        const unsigned ew = __float_as_uint(n0.w);
+        const float adx = __uint_as_float(byte_of(ew, 0) << 23) * idx;
+        const float ady = __uint_as_float(byte_of(ew, 1) << 23) * idy;
+        const float adz = __uint_as_float(byte_of(ew, 2) << 23) * idz;
+        const float bx = (n0.x - r.ox) * idx, by = (n0.y - r.oy) * idy, bz = (n0.z - r.oz) * idz;
+        unsigned hitmask = 0;
 #pragma unroll
-            for (int half = 0; half < 2; half++) {
-                const unsigned meta4 = __float_as_uint(half ? n1.w : n1.z);
-                const unsigned qlx = __float_as_uint(half ? n2.y : n2.x), qly = __float_as_uint(half ? n2.w : n2.z);
-                const unsigned qlz = __float_as_uint(half ? n3.y : n3.x), qhx = __float_as_uint(half ? n3.w : n3.z);
-                const unsigned qhy = __float_as_uint(half ? n4.y : n4.x), qhz = __float_as_uint(half ? n4.w : n4.z);
-                // near / far plane bytes per axis depend on the direction sign
-                const unsigned nx = idx < 0.f ? qhx : qlx, fx = idx < 0.f ? qlx : qhx;
-                const unsigned ny = idy < 0.f ? qhy : qly, fy = idy < 0.f ? qly : qhy;
-                const unsigned nz = idz < 0.f ? qhz : qlz, fz = idz < 0.f ? qlz : qhz;
+        for (int half = 0; half < 2; half++) {
+            const unsigned meta4 = __float_as_uint(half ? n1.w : n1.z);
+            const unsigned qlx = __float_as_uint(half ? n2.y : n2.x), qly = __float_as_uint(half ? n2.w : n2.z);
+            const unsigned qlz = __float_as_uint(half ? n3.y : n3.x), qhx = __float_as_uint(half ? n3.w : n3.z);
+            const unsigned qhy = __float_as_uint(half ? n4.y : n4.x), qhz = __float_as_uint(half ? n4.w : n4.z);
+            // near / far plane bytes per axis depend on the direction sign
+            const unsigned nx = idx < 0.f ? qhx : qlx, fx = idx < 0.f ? qlx : qhx;
+            const unsigned ny = idy < 0.f ? qhy : qly, fy = idy < 0.f ? qly : qhy;
+            const unsigned nz = idz < 0.f ? qhz : qlz, fz = idz < 0.f ? qlz : qhz;
 #pragma unroll
-                for (int j = 0; j < 4; j++) {
-                    const unsigned m = byte_of(meta4, j);
-                    const float t0x = fmaf((float)byte_of(nx, j), adx, bx), t1x = fmaf((float)byte_of(fx, j), adx, bx);
-                    const float t0y = fmaf((float)byte_of(ny, j), ady, by), t1y = fmaf((float)byte_of(fy, j), ady, by);
-                    const float t0z = fmaf((float)byte_of(nz, j), adz, bz), t1z = fmaf((float)byte_of(fz, j), adz, bz);
-                    const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
-                    const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, best_t));
-                    // padded comparison (the planes are computed with a few roundings)
-                    if (m != 0 && t0 - fabsf(t0) * 2e-6f <= t1 + fabsf(t1) * 2e-6f) {
-                        unsigned shift = m & 31u;
-                        if ((m & 0x18u) == 0x18u) shift ^= oct_inv;      // inner child: slot -> traversal priority
-                        hitmask |= (m >> 5) << shift;
-                    }
+            for (int j = 0; j < 4; j++) {
+                const unsigned m = byte_of(meta4, j);
+                const float t0x = fmaf(byte_to_float(nx, j), adx, bx), t1x = fmaf(byte_to_float(fx, j), adx, bx);
+                const float t0y = fmaf(byte_to_float(ny, j), ady, by), t1y = fmaf(byte_to_float(fy, j), ady, by);
+                const float t0z = fmaf(byte_to_float(nz, j), adz, bz), t1z = fmaf(byte_to_float(fz, j), adz, bz);
+                const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
+                const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, best_t));
+                // padded comparison (the planes are computed with a few roundings)
+                if (m != 0 && t0 - fabsf(t0) * 2e-6f <= t1 + fabsf(t1) * 2e-6f) {
+                    unsigned shift = m & 31u;
+                    if ((m & 0x18u) == 0x18u) shift ^= oct_inv;      // inner child: slot -> traversal priority
+                    hitmask |= (m >> 5) << shift;
                 }
             }
-            ng = make_uint2(__float_as_uint(n1.x), (hitmask & 0xff000000u) | (ew >> 24));
-            tg = make_uint2(__float_as_uint(n1.y), hitmask & 0x00ffffffu);
         }
-        while (tg.y) {
-            const int b = __ffs(tg.y) - 1;
-            tg.y &= tg.y - 1;
-            if (COUNT) n_prims++;
-            if (prim<ANY>(sc, (int)tg.x + b)) { found = true; return false; }
+        ng = make_uint2(__float_as_uint(n1.x), (hitmask & 0xff000000u) | (ew >> 24));
+        const uint2 ntg = make_uint2(__float_as_uint(n1.y), hitmask & 0x00ffffffu);
+        if (ntg.y) {
+            if (tg.y == 0u) tg = ntg;
+            else if (sp < LJ_BVH8_STACK) stack[sp++] = ntg;
+            else {                                  // stack full (never seen in practice): test the new group right away
+                unsigned m = ntg.y;
+                while (m) {
+                    const int b = __ffs(m) - 1; m &= m - 1;
+                    if (COUNT) n_prims++;
+                    if (prim<ANY>(sc, (int)ntg.x + b)) return true;
+                }
+            }
         }
-        if (!(ng.y & 0xff000000u)) {
-            if (sp == 0) return false;
-            ng = stack[--sp];
+        refill_from_stack();
+        return false;
+    }
+
+    // Primitive phase: test ONE pending primitive of `tg`.  Requires wants_prim().  Returns true
+    // when an occluder was found (ANY only).
+    template <bool ANY, bool COUNT>
+    LJ_D bool prim_step(const DScene &sc, bool &found) {
+        const int b = __ffs(tg.y) - 1;
+        tg.y &= tg.y - 1;
+        if (COUNT) n_prims++;
+        if (prim<ANY>(sc, (int)tg.x + b)) { found = true; return true; }
+        if (tg.y == 0u) refill_from_stack();
+        return false;
+    }
+
+    // Scalar driver (whole-path engines): run to completion, primitives right after their node.
+    template <bool ANY, bool COUNT>
+    LJ_D bool run(const DScene &sc) {
+        bool found = false;
+        while (true) {
+            while (wants_prim()) if (prim_step<ANY, COUNT>(sc, found)) return true;
+            if (!wants_node()) break;
+            if (node_step<ANY, COUNT>(sc)) return true;
         }
-        return true;
+        return false;
     }
 
     // full hit record of the winning primitive (same arithmetic as during traversal)
@@ -156,14 +210,11 @@ struct Trav8 {
 LJ_D bool trace_closest(const DScene &sc, const RayF &r, Hit *h) {
     if (!sc.bvh8) return traverse_bvh2<false>(sc, r, h);
     Trav8 tv; tv.init(r);
-    bool found = false;
-    while (tv.step<false, false>(sc, found)) {}
+    tv.run<false, false>(sc);
     return tv.finish(sc, h);
 }
 LJ_D bool trace_any(const DScene &sc, const RayF &r) {
     if (!sc.bvh8) return traverse_bvh2<true>(sc, r, nullptr);
     Trav8 tv; tv.init(r);
-    bool found = false;
-    while (tv.step<true, false>(sc, found)) {}
-    return found;
+    return tv.run<true, false>(sc);
 }

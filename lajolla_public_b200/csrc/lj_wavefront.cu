@@ -92,7 +92,6 @@ __global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n
 // mostly empty.  Instead every warp pulls rays from the queue through one atomic work counter
 // and, whenever fewer than REFILL_BELOW lanes are still traversing, hands the idle lanes new
 // rays (warp-aggregated fetch) before stepping on.
-constexpr int REFILL_BELOW = 22;
 enum { W_EXT = 24, W_SHADOW = 25 };     // work counters inside wp.counts
 
 template <bool ANY>
@@ -114,38 +113,51 @@ LJ_D bool warp_fetch(int *work_counter, int n, int &ray_idx, bool &exhausted) {
     return false;
 }
 
+// Phase vote of a trace warp (see lj_traverse8.cuh): lanes either want to open a node or have a
+// primitive pending.  Primitive tests are postponed until at least `prim_thresh` lanes have one
+// (or no lane has node work left), so both phases run with well-filled warps.
+struct TraceTuning { int refill_below, prim_thresh; };
+
 // ---- stage: extend = rtcIntersect1 (intersection.cpp:32) + classification by material kind ----
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters) {
+__global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
     const int n = min(n_upper, wp.counts[Q_EXT]);
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
     unsigned nn = 0, np = 0;
     while (true) {
+        // retire finished lanes together (the hit reconstruction runs with as many lanes as possible)
+        if (ray_idx >= 0 && !tv.active()) {
+            const int slot = wp.ext_slot[ray_idx];
+            Hit h; HitRec hr; int q;
+            if (tv.finish(sc, &h)) {
+                hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
+                q = Q_KIND0 + sc.materials[sc.shapes[h.geom].material_id].kind;
+            } else {
+                hr.t = 0; hr.u = hr.v = 0; hr.geom = -1; hr.prim = -1; hr.ngx = hr.ngy = hr.ngz = 0;
+                q = Q_MISS;
+            }
+            wp.hit[slot] = hr;
+            int *queue = (q == Q_MISS) ? wp.q_miss : wp.q_kind[q - Q_KIND0];
+            queue[queue_push_pos(&wp.counts[q])] = slot;
+            if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
+            ray_idx = -1;
+        }
         if (warp_fetch<false>(&wp.counts[W_EXT], n, ray_idx, exhausted)) tv.init(wp.ext_ray[ray_idx].ray);
         if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
-        const int stop_below = exhausted ? 1 : REFILL_BELOW;
+        const int stop_below = exhausted ? 1 : tune.refill_below;
         while (true) {
-            if (ray_idx >= 0) {
+            const bool live = ray_idx >= 0;
+            const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
+            const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
                 bool found = false;
-                if (!tv.step<false, COUNT>(sc, found)) {
-                    const int slot = wp.ext_slot[ray_idx];
-                    Hit h; HitRec hr; int q;
-                    if (tv.finish(sc, &h)) {
-                        hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
-                        q = Q_KIND0 + sc.materials[sc.shapes[h.geom].material_id].kind;
-                    } else {
-                        hr.t = 0; hr.u = hr.v = 0; hr.geom = -1; hr.prim = -1; hr.ngx = hr.ngy = hr.ngz = 0;
-                        q = Q_MISS;
-                    }
-                    wp.hit[slot] = hr;
-                    int *queue = (q == Q_MISS) ? wp.q_miss : wp.q_kind[q - Q_KIND0];
-                    queue[queue_push_pos(&wp.counts[q])] = slot;
-                    if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
-                    ray_idx = -1;
-                }
+                if (wpr) tv.prim_step<false, COUNT>(sc, found);
+            } else if (mn != 0u) {
+                if (wn) tv.node_step<false, COUNT>(sc);
             }
-            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0)) < stop_below) break;
+            if (__popc(__ballot_sync(0xffffffffu, live && tv.active())) < stop_below) break;
         }
     }
     if (COUNT) { atomicAdd(&trav_counters[0], (unsigned long long)nn); atomicAdd(&trav_counters[1], (unsigned long long)np); }
@@ -153,29 +165,36 @@ __global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_u
 
 // ---- stage: shadow = rtcOccluded1 (intersection.cpp:83) + accumulate the NEE term ----
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_shadow(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters) {
+__global__ void __launch_bounds__(128) k_wf_shadow(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
     const int n = min(n_upper, wp.counts[Q_SHADOW]);
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
+    bool found = false;
     unsigned nn = 0, np = 0;
     while (true) {
-        if (warp_fetch<true>(&wp.counts[W_SHADOW], n, ray_idx, exhausted)) tv.init(wp.shadow[ray_idx].ray);
-        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
-        const int stop_below = exhausted ? 1 : REFILL_BELOW;
-        while (true) {
-            if (ray_idx >= 0) {
-                bool found = false;
-                if (!tv.step<true, COUNT>(sc, found)) {
-                    if (!found) {
-                        const ShadowRec *s = &wp.shadow[ray_idx];
-                        RadRec *ra = &wp.rad[s->slot];
-                        ra->rx += s->cx; ra->ry += s->cy; ra->rz += s->cz;        // path_tracing.h:207
-                    }
-                    if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
-                    ray_idx = -1;
-                }
+        if (ray_idx >= 0 && (found || !tv.active())) {
+            if (!found) {
+                const ShadowRec *s = &wp.shadow[ray_idx];
+                RadRec *ra = &wp.rad[s->slot];
+                ra->rx += s->cx; ra->ry += s->cy; ra->rz += s->cz;        // path_tracing.h:207
             }
-            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0)) < stop_below) break;
+            if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
+            ray_idx = -1;
+        }
+        if (warp_fetch<true>(&wp.counts[W_SHADOW], n, ray_idx, exhausted)) { tv.init(wp.shadow[ray_idx].ray); found = false; }
+        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
+        const int stop_below = exhausted ? 1 : tune.refill_below;
+        while (true) {
+            const bool live = ray_idx >= 0 && !found;
+            const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
+            const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
+                if (wpr) tv.prim_step<true, COUNT>(sc, found);
+            } else if (mn != 0u) {
+                if (wn) { if (tv.node_step<true, COUNT>(sc)) found = true; }
+            }
+            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0 && !found && tv.active())) < stop_below) break;
         }
     }
     if (COUNT) { atomicAdd(&trav_counters[2], (unsigned long long)nn); atomicAdd(&trav_counters[3], (unsigned long long)np); }
@@ -448,7 +467,13 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         for (const lj_material &m : mats) if (m.kind >= 0 && m.kind < LJ_MAT_KIND_COUNT) kind_present[m.kind] = true;
     }
     const int sm = s->ctx->sm_count;
-    const int trace_grid_cap = sm * 16, shade_grid_cap = sm * 16;
+    int trace_grid_cap = sm * 16; const int shade_grid_cap = sm * 16;
+    auto env_int = [](const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; };
+    TraceTuning tune_ext, tune_sh;     // tuning knobs (defaults measured on B200, see profiles/)
+    tune_ext.refill_below = env_int("LJ_REFILL_BELOW", 24); tune_ext.prim_thresh = env_int("LJ_PRIM_THRESH", 8);
+    tune_sh.refill_below = env_int("LJ_REFILL_BELOW_SHADOW", 24); tune_sh.prim_thresh = env_int("LJ_PRIM_THRESH_SHADOW", 4);
+    const int trace_mult = env_int("LJ_TRACE_GRID_MULT", 16);
+    trace_grid_cap = sm * trace_mult;
     const bool trace_iters = getenv("LJ_WF_TRACE") != nullptr;
     const bool stage_timing = (rl.p.flags & 2) != 0 || trace_iters;
     const bool counting = (rl.p.flags & 1) != 0 && d.bvh8 != nullptr;
@@ -472,8 +497,8 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         k_wf_reset<<<1, 32>>>(wp.counts, Q_REGEN, -1, -1);
         if (stage_timing) cudaEventRecord(ev[1]);
         int ext_upper = n_ext + n_regen;
-        if (counting) k_wf_extend<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
-        else k_wf_extend<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
+        if (counting) k_wf_extend<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_ext);
+        else k_wf_extend<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_ext);
         k_wf_reset<<<1, 32>>>(wp.counts, Q_EXT, -1, -1);
         if (stage_timing) cudaEventRecord(ev[2]);
         if (kind_present[0]) launch_shade<0>(d, wp, ext_upper, shade_grid_cap);
@@ -487,8 +512,8 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         if (kind_present[8]) launch_shade<8>(d, wp, ext_upper, shade_grid_cap);
         k_wf_miss<<<grid_for(ext_upper, shade_grid_cap), 128>>>(d, wp, ext_upper);
         if (stage_timing) cudaEventRecord(ev[3]);
-        if (counting) k_wf_shadow<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
-        else k_wf_shadow<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav);
+        if (counting) k_wf_shadow<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_sh);
+        else k_wf_shadow<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_sh);
         k_wf_finish<<<grid_for(ext_upper, shade_grid_cap), 128>>>(wp, ext_upper);
         if (stage_timing) cudaEventRecord(ev[4]);
         // one readback per iteration: queue sizes for the next one (also the ray counts)
