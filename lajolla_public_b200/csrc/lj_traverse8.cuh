@@ -22,10 +22,9 @@
 
 LJ_D unsigned byte_of(unsigned w, int i) { return (w >> (8 * i)) & 0xffu; }
 
-// exact u8 -> f32 without the (quarter-rate) conversion pipe: splice byte j of w into the mantissa
-// of 2^23 with one PRMT, then subtract 2^23 (exact)
-LJ_D float byte_to_float(unsigned w, int j) {
-    return __uint_as_float(__byte_perm(w, 0x4B000000u, 0x7650u + (unsigned)j)) - 8388608.0f;
+// byte j of w spliced into the mantissa of 2^15: returns the float 32768 + byte (exact)
+LJ_D float byte_to_m15(unsigned w, int j) {
+    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404u | ((unsigned)j << 4)));
 }
 
 struct Trav8 {
@@ -112,10 +111,20 @@ struct Trav8 {
         const float4 n0 = __ldg(np), n1 = __ldg(np + 1), n2 = __ldg(np + 2), n3 = __ldg(np + 3), n4 = __ldg(np + 4);
         if (COUNT) n_nodes++;
         const unsigned ew = __float_as_uint(n0.w);
-        const float adx = __uint_as_float(byte_of(ew, 0) << 23) * idx;
-        const float ady = __uint_as_float(byte_of(ew, 1) << 23) * idy;
-        const float adz = __uint_as_float(byte_of(ew, 2) << 23) * idz;
-        const float bx = (n0.x - r.ox) * idx, by = (n0.y - r.oy) * idy, bz = (n0.z - r.oz) * idz;
+        // Child plane along one axis: t = q * A + B with A = 2^e / d, B = (p - o) / d, q the quantised
+        // byte.  The byte is spliced into the mantissa of 2^15 with one PRMT (M = 32768 + q, exact), so
+        // t = fma(M, A, C) with C = B - 32768 A: one PRMT + one FFMA per plane, no int->float conversion.
+        // C carries up to |A|/512 of rounding error per rounding; the near (far) planes are moved out by
+        // |A|/128, i.e. boxes grow by < 1 % of a quantisation step, and stay conservative.
+        const float ax = __uint_as_float(byte_of(ew, 0) << 23) * idx;
+        const float ay = __uint_as_float(byte_of(ew, 1) << 23) * idy;
+        const float az = __uint_as_float(byte_of(ew, 2) << 23) * idz;
+        const float cx = fmaf(-32768.0f, ax, (n0.x - r.ox) * idx);
+        const float cy = fmaf(-32768.0f, ay, (n0.y - r.oy) * idy);
+        const float cz = fmaf(-32768.0f, az, (n0.z - r.oz) * idz);
+        const float px = fabsf(ax) * 0.0078125f, py = fabsf(ay) * 0.0078125f, pz = fabsf(az) * 0.0078125f;
+        const float c0x = cx - px, c1x = cx + px, c0y = cy - py, c1y = cy + py, c0z = cz - pz, c1z = cz + pz;
+        const unsigned oct4 = oct_inv * 0x01010101u;
         unsigned hitmask = 0;
 #pragma unroll
         for (int half = 0; half < 2; half++) {
@@ -127,20 +136,21 @@ struct Trav8 {
             const unsigned nx = idx < 0.f ? qhx : qlx, fx = idx < 0.f ? qlx : qhx;
             const unsigned ny = idy < 0.f ? qhy : qly, fy = idy < 0.f ? qly : qhy;
             const unsigned nz = idz < 0.f ? qhz : qlz, fz = idz < 0.f ? qlz : qhz;
+            // four children at once: which are inner (meta bits 3 and 4 both set), the bit each child
+            // sets in the hit mask (inner: slot -> traversal priority by octant), and the bits it sets
+            const unsigned inner4 = ((meta4 & (meta4 << 1)) & 0x10101010u) >> 4;       // 0x01 per inner child
+            const unsigned index4 = (meta4 ^ (oct4 & (inner4 * 7u))) & 0x1f1f1f1fu;
+            const unsigned bits4 = (meta4 >> 5) & 0x07070707u;                         // 0 for an empty child
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const unsigned m = byte_of(meta4, j);
-                const float t0x = fmaf(byte_to_float(nx, j), adx, bx), t1x = fmaf(byte_to_float(fx, j), adx, bx);
-                const float t0y = fmaf(byte_to_float(ny, j), ady, by), t1y = fmaf(byte_to_float(fy, j), ady, by);
-                const float t0z = fmaf(byte_to_float(nz, j), adz, bz), t1z = fmaf(byte_to_float(fz, j), adz, bz);
+                const float t0x = fmaf(byte_to_m15(nx, j), ax, c0x), t1x = fmaf(byte_to_m15(fx, j), ax, c1x);
+                const float t0y = fmaf(byte_to_m15(ny, j), ay, c0y), t1y = fmaf(byte_to_m15(fy, j), ay, c1y);
+                const float t0z = fmaf(byte_to_m15(nz, j), az, c0z), t1z = fmaf(byte_to_m15(fz, j), az, c1z);
                 const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
                 const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, best_t));
-                // padded comparison (the planes are computed with a few roundings)
-                if (m != 0 && t0 - fabsf(t0) * 2e-6f <= t1 + fabsf(t1) * 2e-6f) {
-                    unsigned shift = m & 31u;
-                    if ((m & 0x18u) == 0x18u) shift ^= oct_inv;      // inner child: slot -> traversal priority
-                    hitmask |= (m >> 5) << shift;
-                }
+                // relative padding on top (B is computed with a few roundings)
+                if (fmaf(fabsf(t0), -2e-6f, t0) <= fmaf(fabsf(t1), 2e-6f, t1))
+                    hitmask |= byte_of(bits4, j) << byte_of(index4, j);
             }
         }
         ng = make_uint2(__float_as_uint(n1.x), (hitmask & 0xff000000u) | (ew >> 24));
