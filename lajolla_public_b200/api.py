@@ -17,7 +17,8 @@ class LjError(RuntimeError):
 
 
 def lib_path():
-    return os.path.join(_HERE, "liblajolla_b200.so")
+    # LJ_LIB: an alternative build of the same library (kernel-variant experiments, tools/)
+    return os.environ.get("LJ_LIB") or os.path.join(_HERE, "liblajolla_b200.so")
 
 
 class RenderParams(C.Structure):

@@ -306,8 +306,11 @@ LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const P
 }
 
 // ---- stage: shade, one launch per material kind present in the scene ----
+#ifndef LJ_SHADE_MIN_BLOCKS
+#define LJ_SHADE_MIN_BLOCKS 4
+#endif
 template <int KIND>
-__global__ void __launch_bounds__(128) k_wf_shade(DScene sc, WfPool wp, int n_upper) {
+__global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc, WfPool wp, int n_upper) {
     int n = min(n_upper, wp.counts[Q_KIND0 + KIND]);
     const int *queue = wp.q_kind[KIND];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
