@@ -44,7 +44,8 @@ struct BSDFSample { d3 dir_out; double eta, roughness; };   // material.h:127-13
 LJ_D d3 sample_cos_hemisphere(d2 rnd) {
     double phi = LJ_TWOPI * rnd.x;
     double tmp = sqrt(clampd(1 - rnd.y, 0.0, 1.0));
-    return mk3(cos(phi) * tmp, sin(phi) * tmp, sqrt(clampd(rnd.y, 0.0, 1.0)));
+    double sp, cp; sincos(phi, &sp, &cp);      // one argument reduction for both; same values as sin() / cos()
+    return mk3(cp * tmp, sp * tmp, sqrt(clampd(rnd.y, 0.0, 1.0)));
 }
 
 // ---- microfacet.h ----
@@ -79,8 +80,9 @@ LJ_D d3 sample_visible_normals_aniso(d3 local_dir_in, double ax, double ay, d2 r
     d3 hemi_dir_in = normalize(mk3(ax * local_dir_in.x, ay * local_dir_in.y, local_dir_in.z));
     double r = sqrt(rnd.x);
     double phi = 2 * LJ_PI * rnd.y;
-    double t1 = r * cos(phi);
-    double t2 = r * sin(phi);
+    double sp, cp; sincos(phi, &sp, &cp);
+    double t1 = r * cp;
+    double t2 = r * sp;
     double s = (1 + hemi_dir_in.z) / 2;
     t2 = (1 - s) * sqrt(1 - t1 * t1) + s * t2;
     d3 disk_N = mk3(t1, t2, sqrt(lmax(0.0, 1 - t1 * t1 - t2 * t2)));

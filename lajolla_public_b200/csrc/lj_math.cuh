@@ -70,7 +70,19 @@ LJ_HD int clampi(int v, int lo, int hi) { return (v < lo) ? lo : ((hi < v) ? hi 
 LJ_HD d3 sqrt3(d3 s) { return mk3(sqrt(lmax(s.x, 0.0)), sqrt(lmax(s.y, 0.0)), sqrt(lmax(s.z, 0.0))); }  // spectrum.h:20-24
 
 LJ_HD double modulo_d(double a, double b) { double r = fmod(a, b); return (r < 0.0) ? r + b : r; }  // lajolla.h:59-62
-LJ_HD int modulo_i(int a, int b) { int r = a % b; return (r < 0) ? r + b : r; }                    // lajolla.h:49-52
+// modulo_d(a, 1): fmod(a, 1) is the fractional part with the sign of a, and a - trunc(a) computes it
+// exactly (same value bit for bit; fmod's software loop is ~100 instructions in f64)
+LJ_HD double modulo_one(double a) {
+    double r = a - trunc(a);
+    if (!(fabs(a) < 4503599627370496.0)) r = fmod(a, 1.0);   // |a| >= 2^52, inf, nan: leave it to fmod
+    return (r < 0.0) ? r + 1.0 : r;
+}
+// lajolla.h:49-52.  Texture wrap indices lie in [-b, 2b): one conditional add/sub gives a % b exactly;
+// anything else takes the integer division.
+LJ_HD int modulo_i(int a, int b) {
+    if (a >= -b && a < 2 * b && b > 0) return a < 0 ? a + b : (a >= b ? a - b : a);
+    int r = a % b; return (r < 0) ? r + b : r;
+}
 
 struct Frame { d3 x, y, n; };
 

@@ -63,15 +63,15 @@ LJ_D T eval_texture_t(const DScene &sc, int tex_id, d2 uv, double footprint) {
         return tex_value(t, t.value, (T *)nullptr);
     } else if (t.kind == LJ_TEX_IMAGE) {
         const lj_image &img = (sizeof(T) == sizeof(double)) ? sc.images1[t.image_id] : sc.images3[t.image_id];
-        double lu = modulo_d(uv.x * t.uscale + t.uoffset, 1.0);
-        double lv = modulo_d(uv.y * t.vscale + t.voffset, 1.0);
+        double lu = modulo_one(uv.x * t.uscale + t.uoffset);
+        double lv = modulo_one(uv.y * t.vscale + t.voffset);
         int wh = img.width[0] > img.height[0] ? img.width[0] : img.height[0];
         double scaled_footprint = wh * lmax(t.uscale, t.vscale) * footprint;
         double level = log2(lmax(scaled_footprint, (double)1e-8f));
         return mip_lookup<T>(sc, img, lu, lv, level);
     } else {
-        double lu = modulo_d(uv.x * t.uscale + t.uoffset, 1.0);
-        double lv = modulo_d(uv.y * t.vscale + t.voffset, 1.0);
+        double lu = modulo_one(uv.x * t.uscale + t.uoffset);
+        double lv = modulo_one(uv.y * t.vscale + t.voffset);
         int x = 2 * modulo_i((int)(lu * 2), 2) - 1;
         int y = 2 * modulo_i((int)(lv * 2), 2) - 1;
         if (x * y == 1) return tex_value(t, t.value, (T *)nullptr);
@@ -214,7 +214,8 @@ LJ_D PointAndNormal sample_point_on_shape(const DScene &sc, const lj_shape &s, d
         double z = 1 - 2 * uv.x;
         double r_ = sqrt(fmax(0.0, 1 - z * z));
         double phi = 2 * LJ_PI * uv.y;
-        d3 offset = mk3(r_ * cos(phi), r_ * sin(phi), z);
+        double sp, cp; sincos(phi, &sp, &cp);
+        d3 offset = mk3(r_ * cp, r_ * sp, z);
         pn.position = center + r * offset;
         pn.normal = offset;
         return pn;
@@ -230,7 +231,8 @@ LJ_D PointAndNormal sample_point_on_shape(const DScene &sc, const lj_shape &s, d
     double ds = dc * cos_elevation - sqrt(lmax(0.0, r * r - dc * dc * sin_elevation * sin_elevation));
     double cos_alpha = (dc * dc + r * r - ds * ds) / (2 * dc * r);
     double sin_alpha = sqrt(lmax(0.0, 1 - cos_alpha * cos_alpha));
-    d3 n_on_sphere = -to_world(frame, mk3(sin_alpha * cos(azimuth), sin_alpha * sin(azimuth), cos_alpha));
+    double saz, caz; sincos(azimuth, &saz, &caz);
+    d3 n_on_sphere = -to_world(frame, mk3(sin_alpha * caz, sin_alpha * saz, cos_alpha));
     pn.position = r * n_on_sphere + center;
     pn.normal = n_on_sphere;
     return pn;

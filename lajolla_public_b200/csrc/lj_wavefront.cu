@@ -49,14 +49,25 @@ LJ_D int queue_push_pos(int *counter) {
     return base + __popc(peers & ((1u << lane) - 1));
 }
 
+// Same, for call sites where every lane pushes to the SAME queue: the converged lanes are the
+// group (no match_any, and the shuffle mask is what the hardware already has).
+LJ_D int queue_push_uniform(int *counter) {
+    const unsigned mask = __activemask();
+    const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
+    int base = 0;
+    if (lane == leader) base = atomicAdd(counter, __popc(mask));
+    base = __shfl_sync(mask, base, leader);
+    return base + __popc(mask & ((1u << lane) - 1));
+}
+
 LJ_D void terminate_path(const WfPool &wp, int slot, d3 radiance) {
     double *a = wp.accum + 3 * (size_t)slot;
     a[0] += radiance.x; a[1] += radiance.y; a[2] += radiance.z;      // render.cpp:92: radiance += path_tracing(...)
-    wp.q_regen[queue_push_pos(&wp.counts[Q_REGEN])] = slot;
+    wp.q_regen[queue_push_uniform(&wp.counts[Q_REGEN])] = slot;
 }
 
 LJ_D void push_extend(const WfPool &wp, int slot, const Ray &r) {
-    int pos = queue_push_pos(&wp.counts[Q_EXT]);
+    int pos = queue_push_uniform(&wp.counts[Q_EXT]);
     ExtRec e; e.ray = to_rayf(r);
     wp.ext_ray[pos] = e;
     wp.ext_slot[pos] = slot;
@@ -247,8 +258,10 @@ namespace {
 template <int KIND>
 LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const PathVertex &vertex, d3 dir_view,
                            Pcg32 &rng, d3 throughput, RayRec &rr, ThrRec &tr, bool &pushed_shadow) {
+    const unsigned grp = __activemask();     // lanes whose path is alive; see `together` in k_wf_shade
     MatParams mat = load_mat_params(sc, vertex);
     mat.kind = KIND;
+    __syncwarp(grp);                         // texture kinds / mip levels differ per lane
     const double eps = sc.eps;
     d2 light_uv; light_uv.x = pcg_real(rng); light_uv.y = pcg_real(rng);
     double light_w = pcg_real(rng);
@@ -256,6 +269,7 @@ LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const P
     int light_id = sample_table1d(sc.light_cdf, sc.num_lights, light_w);
     const lj_light &light = sc.lights[light_id];
     PointAndNormal pl = sample_point_on_light(sc, light, vertex.position, light_uv, shape_w);
+    __syncwarp(grp);
     {
         // G as if unoccluded; the shadow stage zeroes the term when the ray is blocked
         double G; d3 dir_light; double tfar;
@@ -280,11 +294,12 @@ LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const P
                 ShadowRec s;
                 s.ray = to_rayf(make_ray(vertex.position, dir_light, eps, tfar));
                 s.cx = contrib.x; s.cy = contrib.y; s.cz = contrib.z; s.slot = slot; s._pad = 0;
-                wp.shadow[queue_push_pos(&wp.counts[Q_SHADOW])] = s;
+                wp.shadow[queue_push_uniform(&wp.counts[Q_SHADOW])] = s;
                 pushed_shadow = true;
             }
         }
     }
+    __syncwarp(grp);
     d2 bsdf_uv; bsdf_uv.x = pcg_real(rng); bsdf_uv.y = pcg_real(rng);
     double bsdf_w = pcg_real(rng);
     BSDFSample bs;
@@ -314,6 +329,10 @@ __global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc
     int n = min(n_upper, wp.counts[Q_KIND0 + KIND]);
     const int *queue = wp.q_kind[KIND];
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        // lanes that entered this iteration together; __syncwarp(together) below forces them to
+        // reconverge after short divergent blocks (the compiler otherwise runs the long common
+        // tail once per diverged group: 1.7x the instructions, seen in profiles/r01c)
+        const unsigned together = __activemask();
         int slot = queue[i];
         RayRec rr = wp.ray[slot];
         ThrRec tr = wp.thr[slot];
@@ -358,6 +377,7 @@ __global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc
                 tr.nv += 1;
             }
         }
+        __syncwarp(together);
         const int max_depth = sc.options.max_depth;
         if (alive && !(max_depth == -1 || tr.nv <= max_depth + 1)) alive = false;
         bool pushed_shadow = false;
@@ -368,7 +388,7 @@ __global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc
             // radiance and let the finish stage (after the shadow stage) do the accumulation
             ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
             wp.rad[slot] = ra;
-            wp.q_finish[queue_push_pos(&wp.counts[Q_FINISH])] = slot;
+            wp.q_finish[queue_push_uniform(&wp.counts[Q_FINISH])] = slot;
             continue;
         }
         tr.tx = throughput.x; tr.ty = throughput.y; tr.tz = throughput.z;
