@@ -138,6 +138,9 @@ int lj_render_megakernel(lj_scene *s, const RenderLaunch &rl, double *dev_sum, l
 }
 int lj_render_volpath(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st) {
     if (rl.p.rng_mode == LJ_RNG_TILE_STREAMS) return run_tiles<LJ_INTEGRATOR_VOLPATH>(s, rl, dev_sum, st);
+    // versions 1 and 2 are one or two rays per sample: nothing to gain from stages
+    const int v = s->d.options.vol_path_version;
+    if (rl.p.engine == LJ_ENGINE_WAVEFRONT && v != 1 && v != 2 && s->d.bvh8) return lj_render_volwave(s, rl, dev_sum, st);
     return run_mega<LJ_INTEGRATOR_VOLPATH>(s, rl, dev_sum, st);
 }
 

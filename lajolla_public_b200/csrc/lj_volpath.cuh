@@ -194,6 +194,96 @@ LJ_D d3 vol_path_tracing_2(const DScene &sc, int x, int y, Pcg32 &rng, RayCounte
     }
 }
 
+// One NEE segment through a medium: ratio tracking with per-channel spectral MIS
+// (vol_path_tracing.h:354-410).  Shared by the per-lane integrator below and the wavefront stages.
+LJ_D void ratio_track_segment(const DScene &sc, const lj_medium &media, const Ray &shadow_ray, d3 p, d3 dir_light, double next_t,
+                              Pcg32 &rng, d3 &transmittance_light, d3 &p_trans_nee, d3 &p_trans_dir) {
+    d3 majorant = medium_majorant(sc, media, shadow_ray);
+    double u = pcg_real(rng);
+    int channel = clampi((int)(u * 3), 0, 2);
+    double accum_t = 0;
+    int iteration = 0;
+    const double maj_c = comp(majorant, channel);
+    while (true) {
+        if (maj_c <= 0) break;
+        if (iteration >= sc.options.max_null_collisions) break;
+        double t = -log(1 - pcg_real(rng)) / maj_c;
+        double dt = next_t - accum_t;
+        { const double s_ = accum_t + t; accum_t = (next_t < s_) ? next_t : s_; }   // std::min(accum_t + t, next_t)
+        if (t < dt) {
+            d3 pos = p + dir_light * accum_t;
+            d3 sigma_s = medium_sigma_s(sc, media, pos);
+            d3 sigma_a = medium_sigma_a(sc, media, pos);
+            d3 sigma_t = sigma_s + sigma_a;
+            d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
+            d3 real_prob = sigma_t / majorant;
+            d3 e = exp3(-majorant * t);
+            double mx = max3(majorant);
+            transmittance_light = transmittance_light * (e * sigma_n / mx);
+            p_trans_nee = p_trans_nee * (e * majorant / mx);
+            p_trans_dir = p_trans_dir * (e * majorant * (1.0 - real_prob) / mx);
+            if (max3(transmittance_light) <= 0) break;
+        } else {
+            d3 e = exp3(-majorant * dt);
+            transmittance_light = transmittance_light * e;
+            p_trans_nee = p_trans_nee * e;
+            p_trans_dir = p_trans_dir * e;
+            break;
+        }
+        iteration++;
+    }
+}
+
+// Free-flight sampling along the main ray through a medium: delta tracking with null collisions and
+// per-channel spectral MIS (vol_path_tracing.h:556-621).  Moves ray.org to the scattering point (returns
+// true) or to the surface hit; leaves it where it is when the sampled channel's majorant is zero or the
+// null-collision cap is reached (as the reference does).
+LJ_D bool free_flight(const DScene &sc, const lj_medium &media, Ray &ray, double t_hit, d3 hit_position, Pcg32 &rng,
+                      d3 &transmittance, d3 &trans_dir_pdf, d3 &trans_nee_pdf) {
+    d3 majorant = medium_majorant(sc, media, ray);
+    double u = pcg_real(rng);
+    int channel = clampi((int)(u * 3), 0, 2);
+    double accum_t = 0;
+    int iteration = 0;
+    const double maj_c = comp(majorant, channel);
+    while (true) {
+        if (maj_c <= 0) break;
+        if (iteration >= sc.options.max_null_collisions) break;
+        double t = -log(1 - pcg_real(rng)) / maj_c;
+        double dt = t_hit - accum_t;
+        { const double s_ = accum_t + t; accum_t = (t_hit < s_) ? t_hit : s_; }
+        if (t < dt) {
+            d3 p = ray.org + ray.dir * accum_t;
+            d3 sigma_s = medium_sigma_s(sc, media, p);
+            d3 sigma_a = medium_sigma_a(sc, media, p);
+            d3 sigma_t = sigma_s + sigma_a;
+            d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
+            d3 real_prob = sigma_t / majorant;
+            d3 e = exp3(-majorant * t);
+            double mx = max3(majorant);
+            if (pcg_real(rng) < comp(real_prob, channel)) {
+                transmittance = transmittance * (e / mx);
+                trans_dir_pdf = trans_dir_pdf * (e * majorant * real_prob / mx);
+                ray.org = p;
+                return true;
+            } else {
+                transmittance = transmittance * (e * sigma_n / mx);
+                trans_dir_pdf = trans_dir_pdf * (e * majorant * (1.0 - real_prob) / mx);
+                trans_nee_pdf = trans_nee_pdf * (e * majorant / mx);
+            }
+        } else {
+            d3 e = exp3(-majorant * dt);
+            transmittance = transmittance * e;
+            trans_dir_pdf = trans_dir_pdf * e;
+            trans_nee_pdf = trans_nee_pdf * e;
+            ray.org = hit_position;             // dt finite => a hit exists
+            return false;
+        }
+        iteration++;
+    }
+    return false;
+}
+
 // ---- vol_path_tracing.h:299-495 ----
 // Light sample + transmittance to it by ratio tracking through media and index-matched
 // surfaces (closest-hit chain: the reference calls intersect(), not occluded(), :343).
@@ -226,43 +316,8 @@ LJ_D d3 next_event_estimation_final(const DScene &sc, Pcg32 &rng, d3 p, int curr
         double next_t = distance(p, p_prime);
         if (hit) next_t = distance(p, shadow_vertex.position);
 
-        if (shadow_medium != -1) {
-            const lj_medium &media = sc.media[shadow_medium];
-            d3 majorant = medium_majorant(sc, media, shadow_ray);
-            double u = pcg_real(rng);
-            int channel = clampi((int)(u * 3), 0, 2);
-            double accum_t = 0;
-            int iteration = 0;
-            const double maj_c = comp(majorant, channel);
-            while (true) {
-                if (maj_c <= 0) break;
-                if (iteration >= sc.options.max_null_collisions) break;
-                double t = -log(1 - pcg_real(rng)) / maj_c;
-                double dt = next_t - accum_t;
-                { const double s_ = accum_t + t; accum_t = (next_t < s_) ? next_t : s_; }   // std::min(accum_t + t, next_t)
-                if (t < dt) {
-                    d3 pos = p + dir_light * accum_t;
-                    d3 sigma_s = medium_sigma_s(sc, media, pos);
-                    d3 sigma_a = medium_sigma_a(sc, media, pos);
-                    d3 sigma_t = sigma_s + sigma_a;
-                    d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
-                    d3 real_prob = sigma_t / majorant;
-                    d3 e = exp3(-majorant * t);
-                    double mx = max3(majorant);
-                    transmittance_light = transmittance_light * (e * sigma_n / mx);
-                    p_trans_nee = p_trans_nee * (e * majorant / mx);
-                    p_trans_dir = p_trans_dir * (e * majorant * (1.0 - real_prob) / mx);
-                    if (max3(transmittance_light) <= 0) break;
-                } else {
-                    d3 e = exp3(-majorant * dt);
-                    transmittance_light = transmittance_light * e;
-                    p_trans_nee = p_trans_nee * e;
-                    p_trans_dir = p_trans_dir * e;
-                    break;
-                }
-                iteration++;
-            }
-        }
+        if (shadow_medium != -1)
+            ratio_track_segment(sc, sc.media[shadow_medium], shadow_ray, p, dir_light, next_t, rng, transmittance_light, p_trans_nee, p_trans_dir);
 
         if (!hit) break;
         if (shadow_vertex.material_id >= 0) return mk3(0.0);        // blocked by an opaque surface
@@ -328,49 +383,7 @@ LJ_D d3 vol_path_tracing_final(const DScene &sc, int x, int y, Pcg32 &rng, RayCo
         d3 trans_nee_pdf = mk3(1.0);
 
         if (current_medium != -1) {
-            const lj_medium &media = sc.media[current_medium];
-            d3 majorant = medium_majorant(sc, media, ray);
-            double u = pcg_real(rng);
-            int channel = clampi((int)(u * 3), 0, 2);
-            double accum_t = 0;
-            int iteration = 0;
-            const double maj_c = comp(majorant, channel);
-            while (true) {
-                if (maj_c <= 0) break;
-                if (iteration >= sc.options.max_null_collisions) break;
-                double t = -log(1 - pcg_real(rng)) / maj_c;
-                double dt = t_hit - accum_t;
-                { const double s_ = accum_t + t; accum_t = (t_hit < s_) ? t_hit : s_; }
-                if (t < dt) {
-                    d3 p = ray.org + ray.dir * accum_t;
-                    d3 sigma_s = medium_sigma_s(sc, media, p);
-                    d3 sigma_a = medium_sigma_a(sc, media, p);
-                    d3 sigma_t = sigma_s + sigma_a;
-                    d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
-                    d3 real_prob = sigma_t / majorant;
-                    d3 e = exp3(-majorant * t);
-                    double mx = max3(majorant);
-                    if (pcg_real(rng) < comp(real_prob, channel)) {
-                        scatter = true;
-                        transmittance = transmittance * (e / mx);
-                        trans_dir_pdf = trans_dir_pdf * (e * majorant * real_prob / mx);
-                        ray.org = p;
-                        break;
-                    } else {
-                        transmittance = transmittance * (e * sigma_n / mx);
-                        trans_dir_pdf = trans_dir_pdf * (e * majorant * (1.0 - real_prob) / mx);
-                        trans_nee_pdf = trans_nee_pdf * (e * majorant / mx);
-                    }
-                } else {
-                    d3 e = exp3(-majorant * dt);
-                    transmittance = transmittance * e;
-                    trans_dir_pdf = trans_dir_pdf * e;
-                    trans_nee_pdf = trans_nee_pdf * e;
-                    ray.org = vertex.position;             // dt finite => a hit exists
-                    break;
-                }
-                iteration++;
-            }
+            scatter = free_flight(sc, sc.media[current_medium], ray, t_hit, vertex.position, rng, transmittance, trans_dir_pdf, trans_nee_pdf);
             multi_trans_pdf = multi_trans_pdf * trans_dir_pdf;
         } else {
             if (hit) ray.org = vertex.position;

@@ -1,0 +1,590 @@
+// Wavefront engine for the volumetric path integrator (vol_path_tracing.h:503-869, the integrator
+// versions 3-6 forward to; mode B streams).  The reference's loop body is cut at its two ray casts:
+//
+//   generate -> extend (closest hit; main rays AND next-event segments: the reference's NEE walks a
+//               chain of intersect() calls through index-matched surfaces, vol_path_tracing.h:343)
+//            -> main   : free-flight sampling through the current medium (delta tracking with the
+//                        null-collision loop kept inside the stage: it is RNG-serial), emitter MIS,
+//                        index-matched pass-through, depth limit, light sample -> first NEE segment
+//            -> nee    : ratio tracking along one NEE segment, blocked / pass-through / done
+//            -> finish : NEE contribution + spectral MIS, phase-function or BSDF sampling (one kernel
+//                        per material kind), Russian roulette -> next main ray
+//
+// Path slots are regenerated as in lj_wavefront.cu: slot (pixel, k) renders samples s_begin+k,
+// s_begin+k+K, ... and owns its accumulator.  Same RNG draw order, early exits and operation order as
+// lj_volpath.cuh (the one-lane-per-path form used by the parity engines), which this file reuses for
+// media, phase functions and the tracking arithmetic.
+#include "lj_internal.h"
+#include "lj_volpath.cuh"
+#include "lj_wave_common.cuh"
+#include <cstdio>
+#include <cstdlib>
+
+namespace {
+
+enum { VQ_EXT = 0, VQ_REGEN = 1, VQ_MAIN = 2, VQ_NEE = 3, VQ_FIN_MEDIUM = 4, VQ_FIN_KIND0 = 5,
+       VQ_COUNT = VQ_FIN_KIND0 + LJ_MAT_KIND_COUNT, VW_EXT = 24 };
+constexpr int NEE_RAY = (int)0x80000000;    // flag in ext_slot: the ray is an NEE segment
+
+// Per-slot path state that survives between stages (f64, as the reference computes in double).
+struct __align__(16) VolPath {
+    double ox, oy, oz, spread;              // ray.org, ray_diff.spread
+    double dx, dy, dz, eta_scale;           // ray.dir
+    double tx, ty, tz, dir_pdf;             // current_path_throughput, pdf of the latest direction sampling
+    double rx, ry, rz; unsigned long long rng;
+    double mx, my, mz; int medium, bounces; // multi_trans_pdf
+    double cx, cy, cz; int sample, first;   // nee_p_cache
+};                                          // 192 B
+// Next-event state while its segments are traced (vol_path_tracing.h:299-495 locals).
+struct __align__(16) VolNee {
+    double px, py, pz; int light_id, shadow_medium;     // segment origin p
+    double lx, ly, lz; int shadow_bounces, kind;        // dir_light; kind: -1 = medium scatter, else material kind
+    double qx, qy, qz; int blocked, pad0;               // p_prime (point on the light)
+    double nx, ny, nz, pad1;                            // normal at p_prime
+    double ax, ay, az, pad2;                            // transmittance_light
+    double bx, by, bz, pad3;                            // p_trans_nee
+    double ex, ey, ez, pad4;                            // p_trans_dir
+    double gx, gy, gz, pad5;                            // ray.org at the time the main ray was cast (vertex reconstruction)
+};                                                      // 256 B
+
+struct VolPool {
+    int capacity, K;
+    long long npix;
+    VolPath *path; VolNee *nee; HitRec *hit, *nee_hit;
+    double *accum;
+    ExtRec *ext_ray; int *ext_slot;
+    int *q_regen, *q_main, *q_nee, *q_fin_medium, *q_fin_kind[LJ_MAT_KIND_COUNT];
+    int *counts;
+};
+
+LJ_D void vol_terminate(const VolPool &vp, int slot, d3 L) {
+    // render.cpp:140 with vector.h:289-292: a sample is dropped only if ALL channels are non-finite
+    if (isfinite(L.x) || isfinite(L.y) || isfinite(L.z)) {
+        double *a = vp.accum + 3 * (size_t)slot;
+        a[0] += L.x; a[1] += L.y; a[2] += L.z;
+    }
+    vp.q_regen[queue_push_uniform(&vp.counts[VQ_REGEN])] = slot;
+}
+
+LJ_D void vol_push_ray(const VolPool &vp, int slot_and_flag, const Ray &r) {
+    const int pos = queue_push_uniform(&vp.counts[VQ_EXT]);
+    ExtRec e; e.ray = to_rayf(r);
+    vp.ext_ray[pos] = e;
+    vp.ext_slot[pos] = slot_and_flag;
+}
+
+LJ_D Ray vol_main_ray(const DScene &sc, const VolPath &p) {
+    return make_ray(mk3(p.ox, p.oy, p.oz), mk3(p.dx, p.dy, p.dz), sc.eps, INFINITY);   // tnear set once, :513
+}
+
+// ---- stage: generate (vol_path_tracing.h:509-532) ----
+__global__ void __launch_bounds__(128) k_vol_generate(DScene sc, VolPool vp, int n_regen, int s_end, int ntx, int tile_rank, int tile_world) {
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_regen; i += gridDim.x * blockDim.x) {
+        const int slot = vp.q_regen[i];
+        VolPath p = vp.path[slot];
+        const int s = p.sample + vp.K;
+        const int pix = (int)(slot % vp.npix);
+        const int w = sc.camera.width;
+        const int x = pix % w, y = pix / w;
+        bool mine = true;
+        if (tile_world > 0) mine = (((y / 16) * ntx + (x / 16)) % tile_world) == tile_rank;
+        if (s >= s_end || !mine) continue;
+        Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)vp.npix + (unsigned long long)pix);
+        Ray ray = volpath_primary(sc, x, y, rng);
+        p.ox = ray.org.x; p.oy = ray.org.y; p.oz = ray.org.z; p.spread = 0;
+        p.dx = ray.dir.x; p.dy = ray.dir.y; p.dz = ray.dir.z; p.eta_scale = 1;
+        p.tx = p.ty = p.tz = 1; p.dir_pdf = 0;
+        p.rx = p.ry = p.rz = 0; p.rng = rng.state;
+        p.mx = p.my = p.mz = 1; p.medium = sc.camera.medium_id; p.bounces = 0;
+        p.cx = p.cy = p.cz = 0; p.sample = s; p.first = 1;
+        vp.path[slot] = p;
+        vol_push_ray(vp, slot, vol_main_ray(sc, p));
+    }
+}
+
+// ---- stage: extend = intersect() for main rays and NEE segments ----
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_vol_extend(DScene sc, VolPool vp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
+    const int n = min(n_upper, vp.counts[VQ_EXT]);
+    int ray_idx = -1; bool exhausted = false;
+    Trav8 tv;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
+    unsigned nn = 0, np = 0;
+    while (true) {
+        if (ray_idx >= 0 && !tv.active()) {
+            const int tagged = vp.ext_slot[ray_idx];
+            const int slot = tagged & ~NEE_RAY;
+            Hit h; HitRec hr;
+            if (tv.finish(sc, &h)) {
+                hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
+            } else {
+                hr.t = 0; hr.u = hr.v = 0; hr.geom = -1; hr.prim = -1; hr.ngx = hr.ngy = hr.ngz = 0;
+            }
+            const bool is_nee = (tagged & NEE_RAY) != 0;
+            (is_nee ? vp.nee_hit : vp.hit)[slot] = hr;
+            const int q = is_nee ? VQ_NEE : VQ_MAIN;
+            (is_nee ? vp.q_nee : vp.q_main)[queue_push_pos(&vp.counts[q])] = slot;
+            if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
+            ray_idx = -1;
+        }
+        if (warp_fetch<false>(&vp.counts[VW_EXT], n, ray_idx, exhausted)) tv.init(vp.ext_ray[ray_idx].ray);
+        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
+        const int stop_below = exhausted ? 1 : tune.refill_below;
+        while (true) {
+            const bool live = ray_idx >= 0;
+            const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
+            const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
+                bool found = false;
+                if (wpr) tv.prim_step<false, COUNT>(sc, found);
+            } else if (mn != 0u) {
+                if (wn) tv.node_step<false, COUNT>(sc);
+            }
+            if (__popc(__ballot_sync(0xffffffffu, live && tv.active())) < stop_below) break;
+        }
+    }
+    if (COUNT) { atomicAdd(&trav_counters[0], (unsigned long long)nn); atomicAdd(&trav_counters[1], (unsigned long long)np); }
+}
+
+// Russian roulette + next main ray (vol_path_tracing.h:851-864); `p` holds the updated state.
+LJ_D void vol_roulette_and_continue(const DScene &sc, const VolPool &vp, int slot, VolPath &p, Pcg32 &rng) {
+    d3 thr = mk3(p.tx, p.ty, p.tz);
+    if (p.bounces >= sc.options.rr_depth) {
+        const double rr_prob = lmin(max3((1 / p.eta_scale) * thr), 0.95);
+        const double u = pcg_real(rng);
+        if (u > rr_prob) { vol_terminate(vp, slot, mk3(p.rx, p.ry, p.rz)); return; }
+        thr = thr / rr_prob;
+    }
+    p.tx = thr.x; p.ty = thr.y; p.tz = thr.z;
+    p.bounces++;
+    p.rng = rng.state;
+    vp.path[slot] = p;
+    vol_push_ray(vp, slot, vol_main_ray(sc, p));
+}
+
+LJ_D Pcg32 vol_rng(const VolPool &vp, int slot, const VolPath &p) {
+    Pcg32 rng; rng.state = p.rng;
+    rng.inc = (((unsigned long long)p.sample * (unsigned long long)vp.npix + (unsigned long long)(slot % vp.npix)) << 1u) | 1u;
+    return rng;
+}
+LJ_D Hit to_hit(const HitRec &hr) {
+    Hit h; h.t = hr.t; h.u = hr.u; h.v = hr.v; h.geom = hr.geom; h.prim = hr.prim; h.ngx = hr.ngx; h.ngy = hr.ngy; h.ngz = hr.ngz;
+    return h;
+}
+
+// ---- stage: main (vol_path_tracing.h:543-760 up to the light sample of the NEE, :311-320) ----
+__global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_upper) {
+    const int n = min(n_upper, vp.counts[VQ_MAIN]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned together = __activemask();
+        const int slot = vp.q_main[i];
+        VolPath p = vp.path[slot];
+        const HitRec hr = vp.hit[slot];
+        Pcg32 rng = vol_rng(vp, slot, p);
+        Ray ray = vol_main_ray(sc, p);
+        const d3 org0 = ray.org;
+        const bool hit = hr.geom >= 0;
+        PathVertex vertex;
+        vertex.position = mk3(0.0); vertex.material_id = 0; vertex.shape_id = 0;
+        double t_hit = INFINITY;
+        if (hit) {
+            RayDiff rd; rd.radius = 0; rd.spread = p.spread;
+            vertex = make_vertex(sc, ray, to_hit(hr), rd);
+            t_hit = distance(vertex.position, ray.org);
+        }
+        __syncwarp(together);
+        d3 transmittance = mk3(1.0), trans_dir_pdf = mk3(1.0), trans_nee_pdf = mk3(1.0);
+        bool scatter = false;
+        d3 thr = mk3(p.tx, p.ty, p.tz), rad = mk3(p.rx, p.ry, p.rz);
+        d3 multi = mk3(p.mx, p.my, p.mz);
+        bool dead = false;
+        if (p.medium != -1) {
+            scatter = free_flight(sc, sc.media[p.medium], ray, t_hit, vertex.position, rng, transmittance, trans_dir_pdf, trans_nee_pdf);
+            multi = multi * trans_dir_pdf;
+        } else {
+            if (hit) ray.org = vertex.position;
+            else { vol_terminate(vp, slot, mk3(0.0)); dead = true; }          // :637 returns zero, not the radiance so far
+        }
+        __syncwarp(together);
+        if (dead) continue;
+        thr = thr * (transmittance / average(trans_dir_pdf));
+
+        if (!scatter && hit && sc.shapes[vertex.shape_id].area_light_id >= 0) {
+            d3 Le = vertex_emission(sc, vertex, -ray.dir);
+            if (p.bounces == 0) {
+                rad += thr * Le;
+                vol_terminate(vp, slot, rad);
+                continue;
+            }
+            PointAndNormal light_point; light_point.position = vertex.position; light_point.normal = vertex.geometry_normal;
+            const int light_id = sc.shapes[vertex.shape_id].area_light_id;
+            const lj_light &light = sc.lights[light_id];
+            const d3 cache = mk3(p.cx, p.cy, p.cz);
+            d3 pdf_nee = (__ldg(sc.light_pmf + light_id) * pdf_point_on_light(sc, light, light_point, cache)) * trans_nee_pdf;
+            double jacobian = lmax(-dot(-ray.dir, light_point.normal), 0.0) / distance_squared(cache, light_point.position);
+            d3 pdf_phase = (p.dir_pdf * multi) * jacobian;
+            d3 w = (pdf_phase * pdf_phase) / (pdf_phase * pdf_phase + pdf_nee * pdf_nee);
+            rad += thr * Le * w;
+        }
+
+        p.tx = thr.x; p.ty = thr.y; p.tz = thr.z; p.rx = rad.x; p.ry = rad.y; p.rz = rad.z;
+        p.mx = multi.x; p.my = multi.y; p.mz = multi.z;
+        p.ox = ray.org.x; p.oy = ray.org.y; p.oz = ray.org.z;
+        p.first = 0;
+
+        if (!scatter && hit && vertex.material_id == -1) {             // index-matched surface: pass through
+            p.medium = update_medium(vertex, ray.dir, p.medium);
+            p.ox = vertex.position.x; p.oy = vertex.position.y; p.oz = vertex.position.z;
+            p.bounces++;
+            p.rng = rng.state;
+            vp.path[slot] = p;
+            vol_push_ray(vp, slot, vol_main_ray(sc, p));
+            continue;
+        }
+        const int max_depth = sc.options.max_depth;
+        if (p.bounces >= max_depth - 1 && max_depth != -1) { vol_terminate(vp, slot, rad); continue; }
+
+        const bool nee_medium = scatter && p.medium != -1;
+        if (!nee_medium && !hit) {                                     // nothing to scatter on: straight to the roulette
+            vol_roulette_and_continue(sc, vp, slot, p, rng);
+            continue;
+        }
+        // next_event_estimation_final, :311-332: light sample and the first segment
+        d2 light_uv; light_uv.x = pcg_real(rng); light_uv.y = pcg_real(rng);
+        const double light_w = pcg_real(rng);
+        const double shape_w = pcg_real(rng);
+        const int light_id = sample_table1d(sc.light_cdf, sc.num_lights, light_w);
+        const lj_light &light = sc.lights[light_id];
+        PointAndNormal pl = sample_point_on_light(sc, light, ray.org, light_uv, shape_w);
+        const d3 dir_light = normalize(pl.position - ray.org);
+        VolNee ne;
+        ne.px = ray.org.x; ne.py = ray.org.y; ne.pz = ray.org.z; ne.light_id = light_id; ne.shadow_medium = p.medium;
+        ne.lx = dir_light.x; ne.ly = dir_light.y; ne.lz = dir_light.z; ne.shadow_bounces = 0;
+        ne.kind = nee_medium ? -1 : sc.materials[vertex.material_id].kind;
+        ne.qx = pl.position.x; ne.qy = pl.position.y; ne.qz = pl.position.z; ne.blocked = 0; ne.pad0 = 0;
+        ne.nx = pl.normal.x; ne.ny = pl.normal.y; ne.nz = pl.normal.z; ne.pad1 = 0;
+        ne.ax = ne.ay = ne.az = 1; ne.bx = ne.by = ne.bz = 1; ne.ex = ne.ey = ne.ez = 1; ne.pad2 = ne.pad3 = ne.pad4 = ne.pad5 = 0;
+        ne.gx = org0.x; ne.gy = org0.y; ne.gz = org0.z;
+        p.rng = rng.state;
+        vp.path[slot] = p;
+        vp.nee[slot] = ne;
+        const double eps = sc.eps;
+        vol_push_ray(vp, slot | NEE_RAY, make_ray(ray.org, dir_light, eps, (1 - eps) * distance(ray.org, pl.position)));
+    }
+}
+
+// ---- stage: nee = one segment of next_event_estimation_final's loop (:335-439) ----
+__global__ void __launch_bounds__(128) k_vol_nee(DScene sc, VolPool vp, int n_upper) {
+    const int n = min(n_upper, vp.counts[VQ_NEE]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned together = __activemask();
+        const int slot = vp.q_nee[i];
+        VolNee ne = vp.nee[slot];
+        const HitRec hr = vp.nee_hit[slot];
+        VolPath *pp = &vp.path[slot];
+        VolPath p;                           // only rng / sample / bounces are needed here
+        p.rng = pp->rng; p.sample = pp->sample; p.bounces = pp->bounces;
+        Pcg32 rng = vol_rng(vp, slot, p);
+        d3 pos = mk3(ne.px, ne.py, ne.pz);
+        const d3 dir_light = mk3(ne.lx, ne.ly, ne.lz), p_prime = mk3(ne.qx, ne.qy, ne.qz);
+        const double eps = sc.eps;
+        const Ray shadow_ray = make_ray(pos, dir_light, eps, (1 - eps) * distance(pos, p_prime));
+        const bool hit = hr.geom >= 0;
+        PathVertex sv;
+        sv.material_id = 0;
+        double next_t = distance(pos, p_prime);
+        if (hit) {
+            RayDiff rd; rd.radius = 0; rd.spread = 0;
+            sv = make_vertex(sc, shadow_ray, to_hit(hr), rd);
+            next_t = distance(pos, sv.position);
+        }
+        __syncwarp(together);
+        d3 T = mk3(ne.ax, ne.ay, ne.az), ptn = mk3(ne.bx, ne.by, ne.bz), ptd = mk3(ne.ex, ne.ey, ne.ez);
+        if (ne.shadow_medium != -1)
+            ratio_track_segment(sc, sc.media[ne.shadow_medium], shadow_ray, pos, dir_light, next_t, rng, T, ptn, ptd);
+        __syncwarp(together);
+        ne.ax = T.x; ne.ay = T.y; ne.az = T.z; ne.bx = ptn.x; ne.by = ptn.y; ne.bz = ptn.z; ne.ex = ptd.x; ne.ey = ptd.y; ne.ez = ptd.z;
+        pp->rng = rng.state;
+        bool done = false;
+        if (!hit) done = true;
+        else if (sv.material_id >= 0) { ne.blocked = 1; done = true; }
+        else {
+            ne.shadow_bounces++;
+            const int max_depth = sc.options.max_depth;
+            if (max_depth != -1 && p.bounces + ne.shadow_bounces >= max_depth) { ne.blocked = 1; done = true; }
+            else {
+                ne.shadow_medium = update_medium(sv, dir_light, ne.shadow_medium);
+                pos = pos + next_t * dir_light;
+                ne.px = pos.x; ne.py = pos.y; ne.pz = pos.z;
+            }
+        }
+        vp.nee[slot] = ne;
+        if (done) {
+            const int q = ne.kind < 0 ? VQ_FIN_MEDIUM : VQ_FIN_KIND0 + ne.kind;
+            int *queue = ne.kind < 0 ? vp.q_fin_medium : vp.q_fin_kind[ne.kind];
+            queue[queue_push_pos(&vp.counts[q])] = slot;
+        } else {
+            vol_push_ray(vp, slot | NEE_RAY, make_ray(pos, dir_light, eps, (1 - eps) * distance(pos, p_prime)));
+        }
+    }
+}
+
+// NEE contribution once all segments are through (vol_path_tracing.h:443-491).  `evaluated_f` and
+// `pdf_scatter` (phase or BSDF pdf of dir_light) come from the caller; returns contrib * w.
+LJ_D d3 vol_nee_value(const DScene &sc, const VolNee &ne, d3 p_origin, d3 evaluated_f, double pdf_scatter) {
+    const lj_light &light = sc.lights[ne.light_id];
+    PointAndNormal pl; pl.position = mk3(ne.qx, ne.qy, ne.qz); pl.normal = mk3(ne.nx, ne.ny, ne.nz);
+    const d3 dir_light = mk3(ne.lx, ne.ly, ne.lz);
+    const d3 T = mk3(ne.ax, ne.ay, ne.az), ptn = mk3(ne.bx, ne.by, ne.bz), ptd = mk3(ne.ex, ne.ey, ne.ez);
+    d3 Le = light_emission(sc, light, -dir_light, 0.0, pl);
+    double jacobian = lmax(-dot(dir_light, pl.normal), 0.0) / distance_squared(p_origin, pl.position);
+    d3 pdf_nee = (__ldg(sc.light_pmf + ne.light_id) * pdf_point_on_light(sc, light, pl, p_origin)) * ptn;
+    d3 pdf_dir = (pdf_scatter * jacobian) * ptd;
+    d3 contrib = T * evaluated_f * Le * jacobian / average(pdf_nee);
+    d3 w = (pdf_nee * pdf_nee) / (pdf_nee * pdf_nee + pdf_dir * pdf_dir);
+    return contrib * w;
+}
+
+// ---- stage: finish after a scattering event inside a medium (:736-784) ----
+__global__ void __launch_bounds__(128) k_vol_finish_medium(DScene sc, VolPool vp, int n_upper) {
+    const int n = min(n_upper, vp.counts[VQ_FIN_MEDIUM]);
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const int slot = vp.q_fin_medium[i];
+        VolPath p = vp.path[slot];
+        const VolNee ne = vp.nee[slot];
+        Pcg32 rng = vol_rng(vp, slot, p);
+        const d3 org = mk3(p.ox, p.oy, p.oz), dir = mk3(p.dx, p.dy, p.dz);
+        const d3 dir_view = -dir, dir_light = mk3(ne.lx, ne.ly, ne.lz);
+        const lj_medium &media = sc.media[p.medium];
+        d3 nee = mk3(0.0);
+        if (!ne.blocked && max3(mk3(ne.ax, ne.ay, ne.az)) > 0) {
+            pcg_real(rng); pcg_real(rng);                    // the two unused phase_uv draws, :479
+            nee = vol_nee_value(sc, ne, org, phase_eval(media, dir_view, dir_light), phase_pdf(media, dir_view, dir_light));
+        }
+        const d3 sigma_s = medium_sigma_s(sc, media, org);
+        d3 thr = mk3(p.tx, p.ty, p.tz), rad = mk3(p.rx, p.ry, p.rz);
+        rad += thr * sigma_s * nee;
+        if (max3(nee) > 0) { p.cx = org.x; p.cy = org.y; p.cz = org.z; }
+        d2 phase_uv; phase_uv.x = pcg_real(rng); phase_uv.y = pcg_real(rng);
+        const d3 next_dir = phase_sample(media, dir_view, phase_uv);
+        const double ppdf = phase_pdf(media, dir_view, next_dir);
+        thr = thr * (phase_eval(media, dir_view, next_dir) / ppdf * sigma_s);
+        p.dx = next_dir.x; p.dy = next_dir.y; p.dz = next_dir.z;
+        p.dir_pdf = ppdf;
+        p.mx = p.my = p.mz = 1;
+        p.tx = thr.x; p.ty = thr.y; p.tz = thr.z; p.rx = rad.x; p.ry = rad.y; p.rz = rad.z;
+        vol_roulette_and_continue(sc, vp, slot, p, rng);
+    }
+}
+
+// ---- stage: finish at a surface, one launch per material kind (:785-848) ----
+#ifndef LJ_VOL_FINISH_MIN_BLOCKS
+#define LJ_VOL_FINISH_MIN_BLOCKS 4
+#endif
+template <int KIND>
+__global__ void __launch_bounds__(128, LJ_VOL_FINISH_MIN_BLOCKS) k_vol_finish_surface(DScene sc, VolPool vp, int n_upper) {
+    const int n = min(n_upper, vp.counts[VQ_FIN_KIND0 + KIND]);
+    const int *queue = vp.q_fin_kind[KIND];
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        const unsigned together = __activemask();
+        const int slot = queue[i];
+        VolPath p = vp.path[slot];
+        const VolNee ne = vp.nee[slot];
+        const HitRec hr = vp.hit[slot];
+        Pcg32 rng = vol_rng(vp, slot, p);
+        const d3 org = mk3(p.ox, p.oy, p.oz), dir = mk3(p.dx, p.dy, p.dz);
+        const d3 dir_view = -dir, dir_light = mk3(ne.lx, ne.ly, ne.lz);
+        RayDiff rd; rd.radius = 0; rd.spread = p.spread;
+        const PathVertex vertex = make_vertex(sc, make_ray(mk3(ne.gx, ne.gy, ne.gz), dir, sc.eps, INFINITY), to_hit(hr), rd);
+        MatParams mat = load_mat_params(sc, vertex);
+        mat.kind = KIND;
+        __syncwarp(together);
+        d3 nee = mk3(0.0);
+        if (!ne.blocked && max3(mk3(ne.ax, ne.ay, ne.az)) > 0) {
+            const d3 f = bsdf_eval(mat, vertex, dir_view, dir_light);
+            const double pdf_bsdf = bsdf_pdf(mat, vertex, dir_view, dir_light);
+            if (pdf_bsdf > 0) nee = vol_nee_value(sc, ne, org, f, pdf_bsdf);       // :466-469: pdf <= 0 returns zero
+        }
+        __syncwarp(together);
+        d3 thr = mk3(p.tx, p.ty, p.tz), rad = mk3(p.rx, p.ry, p.rz);
+        rad += thr * nee;
+        if (max3(nee) > 0) { p.cx = org.x; p.cy = org.y; p.cz = org.z; }
+        p.rx = rad.x; p.ry = rad.y; p.rz = rad.z;
+        d2 bsdf_uv; bsdf_uv.x = pcg_real(rng); bsdf_uv.y = pcg_real(rng);
+        const double bsdf_w = pcg_real(rng);
+        BSDFSample bs;
+        if (!bsdf_sample(mat, vertex, dir_view, bsdf_uv, bsdf_w, bs)) { vol_terminate(vp, slot, rad); continue; }
+        const d3 dir_bsdf = bs.dir_out;
+        p.dx = dir_bsdf.x; p.dy = dir_bsdf.y; p.dz = dir_bsdf.z;
+        if (bs.eta == 0) {
+            p.spread = rd_reflect(rd, vertex.mean_curvature, bs.roughness);
+        } else {
+            p.spread = rd_refract(rd, vertex.mean_curvature, bs.eta, bs.roughness);
+            p.eta_scale /= (bs.eta * bs.eta);
+            p.medium = update_medium(vertex, dir_bsdf, p.medium);
+        }
+        const d3 f = bsdf_eval(mat, vertex, dir_view, dir_bsdf);
+        const double pdf_bsdf = bsdf_pdf(mat, vertex, dir_view, dir_bsdf);
+        thr = thr * (f / pdf_bsdf);
+        p.tx = thr.x; p.ty = thr.y; p.tz = thr.z;
+        vol_roulette_and_continue(sc, vp, slot, p, rng);
+    }
+}
+
+__global__ void k_vol_reset(int *counts, int a, int b) {
+    if (threadIdx.x == 0) { if (a >= 0) counts[a] = 0; if (b >= 0) counts[b] = 0; }
+}
+__global__ void k_vol_reset_stage_queues(int *counts) {
+    if (threadIdx.x < VQ_COUNT - VQ_MAIN) counts[VQ_MAIN + threadIdx.x] = 0;
+    if (threadIdx.x == 0) counts[VW_EXT] = 0;
+}
+__global__ void k_vol_init(VolPool vp, int s_begin) {
+    for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < vp.capacity; i += (long long)gridDim.x * blockDim.x) {
+        const int k = (int)(i / vp.npix);
+        VolPath p; memset(&p, 0, sizeof p);
+        p.sample = s_begin + k - vp.K;
+        vp.path[i] = p;
+        vp.accum[3 * i] = 0; vp.accum[3 * i + 1] = 0; vp.accum[3 * i + 2] = 0;
+        vp.q_regen[i] = (int)i;
+    }
+}
+__global__ void k_vol_sum(long long npix, int K, const double *accum, double *sum) {
+    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= npix * 3) return;
+    double a = 0;
+    for (int k = 0; k < K; k++) a += accum[(size_t)k * npix * 3 + i];
+    sum[i] = a;
+}
+
+template <int KIND>
+void launch_finish(const DScene &d, const VolPool &vp, int n_upper, int grid_cap) {
+    int grid = (n_upper + 127) / 128;
+    if (grid > grid_cap) grid = grid_cap;
+    if (grid < 1) grid = 1;
+    k_vol_finish_surface<KIND><<<grid, 128>>>(d, vp, n_upper);
+}
+
+} // namespace
+
+static int ensure_vol_pool(lj_scene *s, int capacity, int K, long long npix, VolPool &vp) {
+    const size_t cap = (size_t)capacity;
+    size_t off = 0;
+    auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
+    const size_t o_path = take(cap * sizeof(VolPath)), o_nee = take(cap * sizeof(VolNee));
+    const size_t o_hit = take(cap * sizeof(HitRec)), o_nhit = take(cap * sizeof(HitRec)), o_acc = take(cap * 3 * sizeof(double));
+    const size_t o_er = take(cap * sizeof(ExtRec)), o_es = take(cap * sizeof(int));
+    const size_t o_qr = take(cap * sizeof(int)), o_qm = take(cap * sizeof(int)), o_qn = take(cap * sizeof(int)), o_qfm = take(cap * sizeof(int));
+    size_t o_qk[LJ_MAT_KIND_COUNT];
+    for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) o_qk[k] = take(cap * sizeof(int));
+    const size_t o_cnt = take(64 * sizeof(int));
+    if (off > s->wf_pool_bytes) {
+        if (s->wf_pool) cudaFree(s->wf_pool);
+        s->wf_pool = nullptr; s->wf_pool_bytes = 0;
+        LJ_CUDA(cudaMalloc(&s->wf_pool, off));
+        s->wf_pool_bytes = off;
+    }
+    char *b = (char *)s->wf_pool;
+    vp.capacity = capacity; vp.K = K; vp.npix = npix;
+    vp.path = (VolPath *)(b + o_path); vp.nee = (VolNee *)(b + o_nee); vp.hit = (HitRec *)(b + o_hit); vp.nee_hit = (HitRec *)(b + o_nhit);
+    vp.accum = (double *)(b + o_acc); vp.ext_ray = (ExtRec *)(b + o_er); vp.ext_slot = (int *)(b + o_es);
+    vp.q_regen = (int *)(b + o_qr); vp.q_main = (int *)(b + o_qm); vp.q_nee = (int *)(b + o_qn); vp.q_fin_medium = (int *)(b + o_qfm);
+    for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) vp.q_fin_kind[k] = (int *)(b + o_qk[k]);
+    vp.counts = (int *)(b + o_cnt);
+    return LJ_OK;
+}
+
+int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st) {
+    const DScene &d = s->d;
+    const long long npix = (long long)rl.width * rl.height;
+    const int nsamp = rl.s_end - rl.s_begin;
+    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (1LL << 20);
+    int K = (int)((target + npix - 1) / npix);
+    if (K > nsamp) K = nsamp;
+    if (K < 1) K = 1;
+    if (npix * K > 0x3fffffffLL / 4) { lj_set_error("volumetric wavefront: pool too large"); return LJ_EINVAL; }
+    const int capacity = (int)(npix * K);
+    VolPool vp;
+    int rc = ensure_vol_pool(s, capacity, K, npix, vp);
+    if (rc) return rc;
+
+    bool kind_present[LJ_MAT_KIND_COUNT] = {false};
+    {
+        std::vector<lj_material> mats(d.num_materials);
+        if (d.num_materials) LJ_CUDA(cudaMemcpy(mats.data(), d.materials, sizeof(lj_material) * d.num_materials, cudaMemcpyDeviceToHost));
+        for (const lj_material &m : mats) if (m.kind >= 0 && m.kind < LJ_MAT_KIND_COUNT) kind_present[m.kind] = true;
+    }
+    auto env_int = [](const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; };
+    TraceTuning tune; tune.refill_below = env_int("LJ_REFILL_BELOW", 24); tune.prim_thresh = env_int("LJ_PRIM_THRESH", 8);
+    const int sm = s->ctx->sm_count;
+    const int trace_grid_cap = sm * 16, stage_grid_cap = sm * 16;
+    const bool counting = (rl.p.flags & 1) != 0;
+    const bool stage_timing = (rl.p.flags & 2) != 0;
+    unsigned long long *trav = (unsigned long long *)(vp.counts + 32);
+    cudaEvent_t ev[4];
+    if (stage_timing) for (auto &e : ev) cudaEventCreate(&e);
+
+    LJ_CUDA(cudaMemsetAsync(vp.counts, 0, 64 * sizeof(int)));
+    k_vol_init<<<sm * 8, 256>>>(vp, rl.s_begin);
+    LJ_CUDA(cudaGetLastError());
+    int n_regen = capacity, n_ext = 0;
+    unsigned long long launches = 2, rays_primary = 0, rays_ext = 0;
+    int h_counts[VQ_COUNT];
+    auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
+    while (n_regen > 0 || n_ext > 0) {
+        if (stage_timing) cudaEventRecord(ev[0]);
+        if (n_regen > 0) {
+            k_vol_generate<<<grid_for(n_regen, stage_grid_cap), 128>>>(d, vp, n_regen, rl.s_end, rl.ntx, rl.p.tile_rank, rl.p.tile_world);
+            launches++;
+        }
+        k_vol_reset<<<1, 32>>>(vp.counts, VQ_REGEN, -1);
+        if (stage_timing) cudaEventRecord(ev[1]);
+        const int upper = n_ext + n_regen;
+        if (counting) k_vol_extend<true><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, trav, tune);
+        else k_vol_extend<false><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, trav, tune);
+        k_vol_reset<<<1, 32>>>(vp.counts, VQ_EXT, -1);
+        if (stage_timing) cudaEventRecord(ev[2]);
+        k_vol_main<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
+        k_vol_nee<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
+        k_vol_finish_medium<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
+        if (kind_present[0]) launch_finish<0>(d, vp, upper, stage_grid_cap);
+        if (kind_present[1]) launch_finish<1>(d, vp, upper, stage_grid_cap);
+        if (kind_present[2]) launch_finish<2>(d, vp, upper, stage_grid_cap);
+        if (kind_present[3]) launch_finish<3>(d, vp, upper, stage_grid_cap);
+        if (kind_present[4]) launch_finish<4>(d, vp, upper, stage_grid_cap);
+        if (kind_present[5]) launch_finish<5>(d, vp, upper, stage_grid_cap);
+        if (kind_present[6]) launch_finish<6>(d, vp, upper, stage_grid_cap);
+        if (kind_present[7]) launch_finish<7>(d, vp, upper, stage_grid_cap);
+        if (kind_present[8]) launch_finish<8>(d, vp, upper, stage_grid_cap);
+        if (stage_timing) cudaEventRecord(ev[3]);
+        LJ_CUDA(cudaMemcpy(h_counts, vp.counts, sizeof h_counts, cudaMemcpyDeviceToHost));
+        k_vol_reset_stage_queues<<<1, 32>>>(vp.counts);
+        launches += 8;
+        for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
+        const int traced = h_counts[VQ_MAIN] + h_counts[VQ_NEE];
+        // the generate stage pushed n_regen' <= n_regen primaries this iteration: traced - n_ext of them
+        const int prim_now = traced - n_ext > 0 ? traced - n_ext : 0;
+        rays_primary += prim_now; rays_ext += traced - prim_now;
+        if (stage_timing) {
+            float ms;
+            cudaEventElapsedTime(&ms, ev[0], ev[1]); st->generate_ms += ms;
+            cudaEventElapsedTime(&ms, ev[1], ev[2]); st->extend_ms += ms;
+            cudaEventElapsedTime(&ms, ev[2], ev[3]); st->shade_ms += ms;
+        }
+        n_regen = h_counts[VQ_REGEN];
+        n_ext = h_counts[VQ_EXT];
+        st->iterations++;
+    }
+    k_vol_sum<<<(unsigned)((npix * 3 + 255) / 256), 256>>>(npix, K, vp.accum, dev_sum);
+    LJ_CUDA(cudaGetLastError());
+    if (counting) {
+        unsigned long long h_trav[2];
+        LJ_CUDA(cudaMemcpy(h_trav, trav, sizeof h_trav, cudaMemcpyDeviceToHost));
+        st->nodes_visited = h_trav[0]; st->prims_tested = h_trav[1];
+    }
+    launches++;
+    if (stage_timing) for (auto &e : ev) cudaEventDestroy(e);
+    st->kernel_launches += launches;
+    st->rays_primary += rays_primary; st->rays_extension += rays_ext;
+    st->samples = (uint64_t)npix * (uint64_t)nsamp;
+    return LJ_OK;
+}

@@ -11,6 +11,7 @@
 #include "lj_internal.h"
 #include "lj_materials.cuh"
 #include "lj_traverse8.cuh"
+#include "lj_wave_common.cuh"
 #include <cstdio>
 #include <cstdlib>
 
@@ -21,8 +22,6 @@ enum { Q_EXT = 0, Q_SHADOW = 1, Q_REGEN = 2, Q_FINISH = 3, Q_MISS = 4, Q_KIND0 =
 struct __align__(16) RayRec { double ox, oy, oz, spread, dx, dy, dz, eta_scale; };          // 64 B
 struct __align__(16) ThrRec { double tx, ty, tz, p2, fx, fy, fz; int nv, sample; };          // 64 B
 struct __align__(16) RadRec { double rx, ry, rz; unsigned long long rng; };                  // 32 B
-struct __align__(16) HitRec { float t, u, v; int geom, prim; float ngx, ngy, ngz; };         // 32 B
-struct __align__(16) ExtRec { RayF ray; };                                                   // 32 B
 struct __align__(16) ShadowRec { RayF ray; double cx, cy, cz; int slot, _pad; };             // 64 B
 
 struct WfPool {
@@ -35,30 +34,6 @@ struct WfPool {
     int *q_regen, *q_miss, *q_finish, *q_kind[LJ_MAT_KIND_COUNT];
     int *counts;                // Q_COUNT live queue sizes
 };
-
-// Warp-aggregated queue push: lanes of the calling (possibly partial) warp that push to the
-// same queue elect one leader, which reserves a contiguous range with a single atomicAdd.
-LJ_D int queue_push_pos(int *counter) {
-    unsigned mask = __activemask();
-    unsigned peers = __match_any_sync(mask, (unsigned long long)counter);
-    int leader = __ffs(peers) - 1;
-    int lane = threadIdx.x & 31;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(counter, __popc(peers));
-    base = __shfl_sync(peers, base, leader);
-    return base + __popc(peers & ((1u << lane) - 1));
-}
-
-// Same, for call sites where every lane pushes to the SAME queue: the converged lanes are the
-// group (no match_any, and the shuffle mask is what the hardware already has).
-LJ_D int queue_push_uniform(int *counter) {
-    const unsigned mask = __activemask();
-    const int lane = threadIdx.x & 31, leader = __ffs(mask) - 1;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(counter, __popc(mask));
-    base = __shfl_sync(mask, base, leader);
-    return base + __popc(mask & ((1u << lane) - 1));
-}
 
 LJ_D void terminate_path(const WfPool &wp, int slot, d3 radiance) {
     double *a = wp.accum + 3 * (size_t)slot;
@@ -104,30 +79,6 @@ __global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n
 // and, whenever fewer than REFILL_BELOW lanes are still traversing, hands the idle lanes new
 // rays (warp-aggregated fetch) before stepping on.
 enum { W_EXT = 24, W_SHADOW = 25 };     // work counters inside wp.counts
-
-template <bool ANY>
-LJ_D bool warp_fetch(int *work_counter, int n, int &ray_idx, bool &exhausted) {
-    // called by all 32 lanes; lanes with ray_idx < 0 ask for work
-    const unsigned idle = __ballot_sync(0xffffffffu, ray_idx < 0);
-    if (!idle || exhausted) return false;
-    const int lane = threadIdx.x & 31;
-    const int n_idle = __popc(idle);
-    const int leader = __ffs(idle) - 1;
-    int base = 0;
-    if (lane == leader) base = atomicAdd(work_counter, n_idle);
-    base = __shfl_sync(0xffffffffu, base, leader);
-    if (base + n_idle >= n) exhausted = true;
-    if (ray_idx < 0) {
-        int i = base + __popc(idle & ((1u << lane) - 1u));
-        if (i < n) { ray_idx = i; return true; }
-    }
-    return false;
-}
-
-// Phase vote of a trace warp (see lj_traverse8.cuh): lanes either want to open a node or have a
-// primitive pending.  Primitive tests are postponed until at least `prim_thresh` lanes have one
-// (or no lane has node work left), so both phases run with well-filled warps.
-struct TraceTuning { int refill_below, prim_thresh; };
 
 // ---- stage: extend = rtcIntersect1 (intersection.cpp:32) + classification by material kind ----
 template <bool COUNT>

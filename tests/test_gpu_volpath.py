@@ -36,7 +36,7 @@ def test_volpath_one_spp(gpu, manifest, name, mode):
     img, st = scene.render(RenderParams(spp=1, rng_mode=RNG_TILE_STREAMS if mode == "A" else RNG_SAMPLE_STREAMS))
     scene.close()
     frac = match_fraction(img, ref)
-    meta = e["images"][mode + "1"]
+    meta = e["images"][mode + "1"]   # mode B goes through the default engine (wavefront for versions >= 3)
     print(f"{name} mode {mode}: pixel match {frac:.5f}, tile match {tile_fraction(img, ref):.4f}, rays gpu "
           f"{st.rays_primary + st.rays_extension}+{st.rays_shadow} ref {meta['intersect_rays']}+{meta['occluded_rays']}, "
           f"{st.render_ms:.2f} ms")
@@ -45,15 +45,19 @@ def test_volpath_one_spp(gpu, manifest, name, mode):
 
 
 @pytest.mark.parametrize("name", SCENES)
-def test_volpath_many_spp_same_streams(gpu, manifest, name):
-    from lajolla_public_b200 import RenderParams, RNG_SAMPLE_STREAMS
+@pytest.mark.parametrize("engine", ["wavefront", "megakernel"])
+def test_volpath_many_spp_same_streams(gpu, manifest, name, engine):
+    """16 spp on per-sample streams through both engines: the staged wavefront engine (lj_volwave.cu;
+    versions 1 and 2 stay on the per-lane kernel) and the one-lane-per-path megakernel"""
+    from lajolla_public_b200 import RenderParams, RNG_SAMPLE_STREAMS, ENGINE_WAVEFRONT, ENGINE_MEGAKERNEL
     d, e, scene = load(gpu, manifest, name)
     ref = np.load(os.path.join(d, f"{name}_B16.npy"))
-    img, st = scene.render(RenderParams(spp=16, rng_mode=RNG_SAMPLE_STREAMS))
+    img, st = scene.render(RenderParams(spp=16, rng_mode=RNG_SAMPLE_STREAMS,
+                                        engine=ENGINE_WAVEFRONT if engine == "wavefront" else ENGINE_MEGAKERNEL))
     scene.close()
     frac = match_fraction(img, ref)
     rmse = float(np.sqrt(np.mean((img - ref) ** 2)))
-    print(f"{name}: RMSE {rmse:.3e}, pixel match {frac:.5f}, mean gpu {img.mean():.6f} ref {ref.mean():.6f}, "
+    print(f"{name} {engine}: RMSE {rmse:.3e}, pixel match {frac:.5f}, mean gpu {img.mean():.6f} ref {ref.mean():.6f}, "
           f"{st.samples / st.render_ms * 1e-3:.2f} Msamples/s, {st.rays / st.render_ms * 1e-3:.1f} Mrays/s")
     assert frac >= 0.85
     assert abs(float(img.mean()) - float(ref.mean())) <= 0.02 * float(ref.mean())
