@@ -8,12 +8,13 @@
 
 #include <cfloat>
 #include <cstdio>
+#include <cstdlib>
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { snprintf(err, 256, "%s: %s", #x, cudaGetErrorString(e_)); return -1; } } while (0)
 
 namespace {
 
-constexpr int MAX_LEAF = 3;   // primitives per leaf slot (unary count in 3 bits)
+constexpr int MAX_LEAF_CAP = 3;   // primitives per leaf slot (unary count in 3 bits)
 
 struct Work { int node2; int node8; };
 
@@ -31,7 +32,7 @@ __global__ void k_collapse_level(const Work *items, int n_items, Work *items_out
                                  const int *left, const int *right, const float4 *node_lo, const float4 *node_hi,
                                  const int *count, const int *sorted_prim,
                                  const float4 *prim_lo, const float4 *prim_hi, const float4 *tri_verts,
-                                 Bvh8Node *nodes8, int *node_counter, float4 *tri_verts8, int *prim_counter, int n_prims_total) {
+                                 Bvh8Node *nodes8, int *node_counter, float4 *tri_verts8, int *prim_counter, int n_prims_total, int MAX_LEAF) {
     int wi = blockIdx.x * blockDim.x + threadIdx.x;
     if (wi >= n_items) return;
     Work w = items[wi];
@@ -135,7 +136,7 @@ __global__ void k_collapse_level(const Work *items, int n_items, Work *items_out
                 unsigned unary = (1u << cnt) - 1u;
                 nd.meta[s] = (uint8_t)((unary << 5) | prim_off);
                 // enumerate the (at most MAX_LEAF) leaves of this small subtree
-                int stk[MAX_LEAF + 1]; int sp = 0, k = 0;
+                int stk[MAX_LEAF_CAP + 1]; int sp = 0, k = 0;
                 stk[sp++] = c;
                 while (sp) {
                     int x = stk[--sp];
@@ -180,13 +181,15 @@ int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left,
     CK(cudaMemcpy(counters, h_counters, sizeof h_counters, cudaMemcpyHostToDevice));
     Work root; root.node2 = (n >= 2) ? root2 : ~0; root.node8 = 0;
     CK(cudaMemcpy(q0, &root, sizeof root, cudaMemcpyHostToDevice));
+    int max_leaf = MAX_LEAF_CAP;      // LJ_MAX_LEAF: experiment knob (1..3)
+    if (const char *e = getenv("LJ_MAX_LEAF")) { int v = atoi(e); if (v >= 1 && v <= MAX_LEAF_CAP) max_leaf = v; }
     int n_items = 1;
     int levels = 0;
     while (n_items > 0) {
         CK(cudaMemset(counters + 2, 0, sizeof(int)));
         k_collapse_level<<<(n_items + 63) / 64, 64>>>(q0, n_items, q1, counters + 2, left, right, node_lo, node_hi,
                                                        count, sorted_prim, prim_lo, prim_hi, tri_verts,
-                                                       out.bvh8, counters, out.tri_verts8, counters + 1, n);
+                                                       out.bvh8, counters, out.tri_verts8, counters + 1, n, max_leaf);
         CK(cudaGetLastError());
         CK(cudaMemcpy(h_counters, counters, sizeof h_counters, cudaMemcpyDeviceToHost));
         n_items = h_counters[2];

@@ -84,6 +84,20 @@ LJ_D d3 medium_sigma_a(const DScene &sc, const lj_medium &m, d3 p) {
     return density * (1.0 - albedo);
 }
 
+// sigma_s and sigma_a at one point: both are functions of the same two grid lookups (density, albedo),
+// which the reference performs twice (media/heterogeneous.inl:11-21); identical values, half the gathers.
+LJ_D void medium_sigma_sa(const DScene &sc, const lj_medium &m, d3 p, d3 &sigma_s, d3 &sigma_a) {
+    if (m.kind == LJ_MEDIUM_HOMOGENEOUS) {
+        sigma_s = mk3(m.sigma_s[0], m.sigma_s[1], m.sigma_s[2]);
+        sigma_a = mk3(m.sigma_a[0], m.sigma_a[1], m.sigma_a[2]);
+        return;
+    }
+    d3 density = volume_lookup(sc, m.density, p);
+    d3 albedo = volume_lookup(sc, m.albedo, p);
+    sigma_s = density * albedo;
+    sigma_a = density * (1.0 - albedo);
+}
+
 // ---- phase functions (phase_functions/isotropic.inl, henyeygreenstein.inl) ----
 LJ_D double phase_value(const lj_medium &m, d3 dir_in, d3 dir_out) {
     if (m.phase_kind == LJ_PHASE_ISOTROPIC) return LJ_INVFOURPI;
@@ -212,8 +226,8 @@ LJ_D void ratio_track_segment(const DScene &sc, const lj_medium &media, const Ra
         { const double s_ = accum_t + t; accum_t = (next_t < s_) ? next_t : s_; }   // std::min(accum_t + t, next_t)
         if (t < dt) {
             d3 pos = p + dir_light * accum_t;
-            d3 sigma_s = medium_sigma_s(sc, media, pos);
-            d3 sigma_a = medium_sigma_a(sc, media, pos);
+            d3 sigma_s, sigma_a;
+            medium_sigma_sa(sc, media, pos, sigma_s, sigma_a);
             d3 sigma_t = sigma_s + sigma_a;
             d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
             d3 real_prob = sigma_t / majorant;
@@ -254,8 +268,8 @@ LJ_D bool free_flight(const DScene &sc, const lj_medium &media, Ray &ray, double
         { const double s_ = accum_t + t; accum_t = (t_hit < s_) ? t_hit : s_; }
         if (t < dt) {
             d3 p = ray.org + ray.dir * accum_t;
-            d3 sigma_s = medium_sigma_s(sc, media, p);
-            d3 sigma_a = medium_sigma_a(sc, media, p);
+            d3 sigma_s, sigma_a;
+            medium_sigma_sa(sc, media, p, sigma_s, sigma_a);
             d3 sigma_t = sigma_s + sigma_a;
             d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
             d3 real_prob = sigma_t / majorant;
