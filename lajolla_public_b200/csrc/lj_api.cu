@@ -87,7 +87,7 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
     double e = desc->bounds_radius * 1e-5;            // scene.h:99-105
     d.eps = e < 0.01 ? e : 0.01;
     d.envmap_light_id = desc->envmap_light_id;
-    d.num_lights = (int)desc->num_lights; d.num_shapes = (int)desc->num_shapes; d.num_materials = (int)desc->num_materials;
+    d.num_lights = (int)desc->num_lights; d.num_shapes = (int)desc->num_shapes; d.num_materials = (int)desc->num_materials; d.num_media = (int)desc->num_media;
 #define UP(field, cnt) if ((rc = upload(s, desc->field, (size_t)(cnt), &d.field)) != LJ_OK) { lj_scene_destroy(s); return rc; }
     UP(shapes, desc->num_shapes) UP(lights, desc->num_lights) UP(materials, desc->num_materials) UP(media, desc->num_media)
     UP(textures, desc->num_textures) UP(images1, desc->num_images1) UP(images3, desc->num_images3)

@@ -32,7 +32,7 @@ struct DScene {
     double bounds_radius;
     double eps;                 // get_shadow_epsilon == get_intersection_epsilon, scene.h:99-105
     int envmap_light_id;
-    int num_lights, num_shapes, num_materials;
+    int num_lights, num_shapes, num_materials, num_media;
 
     const lj_shape *shapes;
     const lj_light *lights;

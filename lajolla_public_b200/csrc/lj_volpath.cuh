@@ -208,44 +208,98 @@ LJ_D d3 vol_path_tracing_2(const DScene &sc, int x, int y, Pcg32 &rng, RayCounte
     }
 }
 
-// One NEE segment through a medium: ratio tracking with per-channel spectral MIS
-// (vol_path_tracing.h:354-410).  Shared by the per-lane integrator below and the wavefront stages.
+// Tracking loops in begin / step form, so that the per-lane integrator (run to completion) and the
+// wavefront tracking kernel (lj_volwave.cu: one collision per lane per warp iteration, finished lanes
+// refilled) execute the very same arithmetic.
+struct TrackState { d3 majorant; double maj_c, accum_t; int channel, iteration; bool active; };
+
+LJ_D void track_begin(const DScene &sc, const lj_medium &media, const Ray &ray, Pcg32 &rng, TrackState &ts) {
+    ts.majorant = medium_majorant(sc, media, ray);
+    double u = pcg_real(rng);
+    ts.channel = clampi((int)(u * 3), 0, 2);
+    ts.accum_t = 0;
+    ts.iteration = 0;
+    ts.maj_c = comp(ts.majorant, ts.channel);
+    ts.active = !(ts.maj_c <= 0) && !(ts.iteration >= sc.options.max_null_collisions);
+}
+
+// One iteration of the NEE ratio-tracking loop (vol_path_tracing.h:364-408).
+LJ_D void ratio_track_step(const DScene &sc, const lj_medium &media, d3 p, d3 dir_light, double next_t, Pcg32 &rng, TrackState &ts,
+                           d3 &transmittance_light, d3 &p_trans_nee, d3 &p_trans_dir) {
+    const d3 majorant = ts.majorant;
+    double t = -log(1 - pcg_real(rng)) / ts.maj_c;
+    double dt = next_t - ts.accum_t;
+    { const double s_ = ts.accum_t + t; ts.accum_t = (next_t < s_) ? next_t : s_; }   // std::min(accum_t + t, next_t)
+    if (t < dt) {
+        d3 pos = p + dir_light * ts.accum_t;
+        d3 sigma_s, sigma_a;
+        medium_sigma_sa(sc, media, pos, sigma_s, sigma_a);
+        d3 sigma_t = sigma_s + sigma_a;
+        d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
+        d3 real_prob = sigma_t / majorant;
+        d3 e = exp3(-majorant * t);
+        double mx = max3(majorant);
+        transmittance_light = transmittance_light * (e * sigma_n / mx);
+        p_trans_nee = p_trans_nee * (e * majorant / mx);
+        p_trans_dir = p_trans_dir * (e * majorant * (1.0 - real_prob) / mx);
+        if (max3(transmittance_light) <= 0) { ts.active = false; return; }
+    } else {
+        d3 e = exp3(-majorant * dt);
+        transmittance_light = transmittance_light * e;
+        p_trans_nee = p_trans_nee * e;
+        p_trans_dir = p_trans_dir * e;
+        ts.active = false; return;
+    }
+    ts.iteration++;
+    if (ts.iteration >= sc.options.max_null_collisions) ts.active = false;
+}
+
+// One NEE segment through a medium: ratio tracking with per-channel spectral MIS (vol_path_tracing.h:354-410).
 LJ_D void ratio_track_segment(const DScene &sc, const lj_medium &media, const Ray &shadow_ray, d3 p, d3 dir_light, double next_t,
                               Pcg32 &rng, d3 &transmittance_light, d3 &p_trans_nee, d3 &p_trans_dir) {
-    d3 majorant = medium_majorant(sc, media, shadow_ray);
-    double u = pcg_real(rng);
-    int channel = clampi((int)(u * 3), 0, 2);
-    double accum_t = 0;
-    int iteration = 0;
-    const double maj_c = comp(majorant, channel);
-    while (true) {
-        if (maj_c <= 0) break;
-        if (iteration >= sc.options.max_null_collisions) break;
-        double t = -log(1 - pcg_real(rng)) / maj_c;
-        double dt = next_t - accum_t;
-        { const double s_ = accum_t + t; accum_t = (next_t < s_) ? next_t : s_; }   // std::min(accum_t + t, next_t)
-        if (t < dt) {
-            d3 pos = p + dir_light * accum_t;
-            d3 sigma_s, sigma_a;
-            medium_sigma_sa(sc, media, pos, sigma_s, sigma_a);
-            d3 sigma_t = sigma_s + sigma_a;
-            d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
-            d3 real_prob = sigma_t / majorant;
-            d3 e = exp3(-majorant * t);
-            double mx = max3(majorant);
-            transmittance_light = transmittance_light * (e * sigma_n / mx);
-            p_trans_nee = p_trans_nee * (e * majorant / mx);
-            p_trans_dir = p_trans_dir * (e * majorant * (1.0 - real_prob) / mx);
-            if (max3(transmittance_light) <= 0) break;
+    TrackState ts;
+    track_begin(sc, media, shadow_ray, rng, ts);
+    while (ts.active) ratio_track_step(sc, media, p, dir_light, next_t, rng, ts, transmittance_light, p_trans_nee, p_trans_dir);
+}
+
+// One iteration of the free-flight (delta tracking) loop (vol_path_tracing.h:565-621).  Sets `scatter`
+// and moves ray.org on a real collision or when the surface is reached.
+LJ_D void free_flight_step(const DScene &sc, const lj_medium &media, Ray &ray, double t_hit, d3 hit_position, Pcg32 &rng, TrackState &ts,
+                           d3 &transmittance, d3 &trans_dir_pdf, d3 &trans_nee_pdf, bool &scatter) {
+    const d3 majorant = ts.majorant;
+    double t = -log(1 - pcg_real(rng)) / ts.maj_c;
+    double dt = t_hit - ts.accum_t;
+    { const double s_ = ts.accum_t + t; ts.accum_t = (t_hit < s_) ? t_hit : s_; }
+    if (t < dt) {
+        d3 p = ray.org + ray.dir * ts.accum_t;
+        d3 sigma_s, sigma_a;
+        medium_sigma_sa(sc, media, p, sigma_s, sigma_a);
+        d3 sigma_t = sigma_s + sigma_a;
+        d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
+        d3 real_prob = sigma_t / majorant;
+        d3 e = exp3(-majorant * t);
+        double mx = max3(majorant);
+        if (pcg_real(rng) < comp(real_prob, ts.channel)) {
+            transmittance = transmittance * (e / mx);
+            trans_dir_pdf = trans_dir_pdf * (e * majorant * real_prob / mx);
+            ray.org = p;
+            scatter = true;
+            ts.active = false; return;
         } else {
-            d3 e = exp3(-majorant * dt);
-            transmittance_light = transmittance_light * e;
-            p_trans_nee = p_trans_nee * e;
-            p_trans_dir = p_trans_dir * e;
-            break;
+            transmittance = transmittance * (e * sigma_n / mx);
+            trans_dir_pdf = trans_dir_pdf * (e * majorant * (1.0 - real_prob) / mx);
+            trans_nee_pdf = trans_nee_pdf * (e * majorant / mx);
         }
-        iteration++;
+    } else {
+        d3 e = exp3(-majorant * dt);
+        transmittance = transmittance * e;
+        trans_dir_pdf = trans_dir_pdf * e;
+        trans_nee_pdf = trans_nee_pdf * e;
+        ray.org = hit_position;             // dt finite => a hit exists
+        ts.active = false; return;
     }
+    ts.iteration++;
+    if (ts.iteration >= sc.options.max_null_collisions) ts.active = false;
 }
 
 // Free-flight sampling along the main ray through a medium: delta tracking with null collisions and
@@ -254,48 +308,11 @@ LJ_D void ratio_track_segment(const DScene &sc, const lj_medium &media, const Ra
 // null-collision cap is reached (as the reference does).
 LJ_D bool free_flight(const DScene &sc, const lj_medium &media, Ray &ray, double t_hit, d3 hit_position, Pcg32 &rng,
                       d3 &transmittance, d3 &trans_dir_pdf, d3 &trans_nee_pdf) {
-    d3 majorant = medium_majorant(sc, media, ray);
-    double u = pcg_real(rng);
-    int channel = clampi((int)(u * 3), 0, 2);
-    double accum_t = 0;
-    int iteration = 0;
-    const double maj_c = comp(majorant, channel);
-    while (true) {
-        if (maj_c <= 0) break;
-        if (iteration >= sc.options.max_null_collisions) break;
-        double t = -log(1 - pcg_real(rng)) / maj_c;
-        double dt = t_hit - accum_t;
-        { const double s_ = accum_t + t; accum_t = (t_hit < s_) ? t_hit : s_; }
-        if (t < dt) {
-            d3 p = ray.org + ray.dir * accum_t;
-            d3 sigma_s, sigma_a;
-            medium_sigma_sa(sc, media, p, sigma_s, sigma_a);
-            d3 sigma_t = sigma_s + sigma_a;
-            d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
-            d3 real_prob = sigma_t / majorant;
-            d3 e = exp3(-majorant * t);
-            double mx = max3(majorant);
-            if (pcg_real(rng) < comp(real_prob, channel)) {
-                transmittance = transmittance * (e / mx);
-                trans_dir_pdf = trans_dir_pdf * (e * majorant * real_prob / mx);
-                ray.org = p;
-                return true;
-            } else {
-                transmittance = transmittance * (e * sigma_n / mx);
-                trans_dir_pdf = trans_dir_pdf * (e * majorant * (1.0 - real_prob) / mx);
-                trans_nee_pdf = trans_nee_pdf * (e * majorant / mx);
-            }
-        } else {
-            d3 e = exp3(-majorant * dt);
-            transmittance = transmittance * e;
-            trans_dir_pdf = trans_dir_pdf * e;
-            trans_nee_pdf = trans_nee_pdf * e;
-            ray.org = hit_position;             // dt finite => a hit exists
-            return false;
-        }
-        iteration++;
-    }
-    return false;
+    TrackState ts;
+    track_begin(sc, media, ray, rng, ts);
+    bool scatter = false;
+    while (ts.active) free_flight_step(sc, media, ray, t_hit, hit_position, rng, ts, transmittance, trans_dir_pdf, trans_nee_pdf, scatter);
+    return scatter;
 }
 
 // ---- vol_path_tracing.h:299-495 ----

@@ -23,7 +23,7 @@
 namespace {
 
 enum { VQ_EXT = 0, VQ_REGEN = 1, VQ_MAIN = 2, VQ_NEE = 3, VQ_FIN_MEDIUM = 4, VQ_FIN_KIND0 = 5,
-       VQ_COUNT = VQ_FIN_KIND0 + LJ_MAT_KIND_COUNT, VW_EXT = 24 };
+       VQ_COUNT = VQ_FIN_KIND0 + LJ_MAT_KIND_COUNT, VW_EXT = 24, VW_TRACK_MAIN = 25, VW_TRACK_NEE = 26 };
 constexpr int NEE_RAY = (int)0x80000000;    // flag in ext_slot: the ray is an NEE segment
 
 // Per-slot path state that survives between stages (f64, as the reference computes in double).
@@ -47,10 +47,18 @@ struct __align__(16) VolNee {
     double gx, gy, gz, pad5;                            // ray.org at the time the main ray was cast (vertex reconstruction)
 };                                                      // 256 B
 
+// Result of the free-flight tracking of a main ray (written by k_vol_track<false>, read by k_vol_main).
+struct __align__(16) VolTrack {
+    double tx, ty, tz, ox;                  // transmittance, new ray.org.x
+    double dx, dy, dz, oy;                  // trans_dir_pdf, new ray.org.y
+    double nx, ny, nz, oz;                  // trans_nee_pdf, new ray.org.z
+    int scatter, pad0, pad1, pad2;
+};                                          // 112 B
+
 struct VolPool {
     int capacity, K;
     long long npix;
-    VolPath *path; VolNee *nee; HitRec *hit, *nee_hit;
+    VolPath *path; VolNee *nee; HitRec *hit, *nee_hit; VolTrack *track;
     double *accum;
     ExtRec *ext_ray; int *ext_slot;
     int *q_regen, *q_main, *q_nee, *q_fin_medium, *q_fin_kind[LJ_MAT_KIND_COUNT];
@@ -172,6 +180,82 @@ LJ_D Hit to_hit(const HitRec &hr) {
     return h;
 }
 
+// ---- stage: track = the RNG-serial collision loops, one collision per lane per warp iteration ----
+// NEE = false: free-flight sampling of the main rays (vol_path_tracing.h:556-626) -> VolTrack
+// NEE = true : ratio tracking of one NEE segment (:354-410) -> transmittance / pdf products in VolNee
+// Segments need between zero and max_null_collisions iterations, so a warp that walked its 32 segments
+// to the end would idle most lanes; instead a lane whose loop is over is retired and handed the next
+// segment from the queue (same scheme as the trace kernels).  The arithmetic is lj_volpath.cuh's.
+// Grid media only: in a homogeneous medium the majorant is sigma_t itself, the loop ends at the first collision
+// and stays inline in k_vol_main / k_vol_nee.
+LJ_D int tracked_medium(const DScene &sc, int medium) {
+    return (medium != -1 && sc.media[medium].kind == LJ_MEDIUM_HETEROGENEOUS) ? medium : -1;
+}
+
+template <bool NEE>
+__global__ void __launch_bounds__(128) k_vol_track(DScene sc, VolPool vp, int n_upper, int refill_below) {
+    const int n = min(n_upper, vp.counts[NEE ? VQ_NEE : VQ_MAIN]);
+    const int *queue = NEE ? vp.q_nee : vp.q_main;
+    int item = -1, slot = -1, medium = -1; bool exhausted = false;     // medium = -1: nothing to track for this item
+    TrackState ts; ts.active = false;
+    Pcg32 rng; rng.state = 0; rng.inc = 1;
+    Ray ray = make_ray(mk3(0.0), mk3(0.0), 0, 0);       // main ray, or the shadow segment
+    double t_end = 0; d3 hit_position = mk3(0.0);
+    d3 A = mk3(1.0), Bv = mk3(1.0), Cv = mk3(1.0);      // main: transmittance, dir pdf, nee pdf; NEE: T_light, p_trans_nee, p_trans_dir
+    bool scatter = false;
+    while (true) {
+        if (item >= 0 && !ts.active) {                  // retire
+            if (medium != -1) {
+                if (NEE) {
+                    VolNee *ne = &vp.nee[slot];
+                    ne->ax = A.x; ne->ay = A.y; ne->az = A.z; ne->bx = Bv.x; ne->by = Bv.y; ne->bz = Bv.z; ne->ex = Cv.x; ne->ey = Cv.y; ne->ez = Cv.z;
+                } else {
+                    VolTrack tr;
+                    tr.tx = A.x; tr.ty = A.y; tr.tz = A.z; tr.dx = Bv.x; tr.dy = Bv.y; tr.dz = Bv.z; tr.nx = Cv.x; tr.ny = Cv.y; tr.nz = Cv.z;
+                    tr.ox = ray.org.x; tr.oy = ray.org.y; tr.oz = ray.org.z; tr.scatter = scatter ? 1 : 0; tr.pad0 = tr.pad1 = tr.pad2 = 0;
+                    vp.track[slot] = tr;
+                }
+                vp.path[slot].rng = rng.state;
+            }
+            item = -1;
+        }
+        if (warp_fetch<false>(&vp.counts[NEE ? VW_TRACK_NEE : VW_TRACK_MAIN], n, item, exhausted)) {
+            slot = queue[item];
+            const VolPath *pp = &vp.path[slot];
+            rng.state = pp->rng;
+            rng.inc = (((unsigned long long)pp->sample * (unsigned long long)vp.npix + (unsigned long long)(slot % vp.npix)) << 1u) | 1u;
+            scatter = false; ts.active = false;
+            if (NEE) {
+                const VolNee ne = vp.nee[slot];
+                const HitRec hr = vp.nee_hit[slot];
+                medium = tracked_medium(sc, ne.shadow_medium);
+                const d3 pos = mk3(ne.px, ne.py, ne.pz), dir_light = mk3(ne.lx, ne.ly, ne.lz), p_prime = mk3(ne.qx, ne.qy, ne.qz);
+                ray = make_ray(pos, dir_light, sc.eps, (1 - sc.eps) * distance(pos, p_prime));
+                t_end = distance(pos, p_prime);
+                if (hr.geom >= 0) t_end = distance(pos, ray.org + ray.dir * (double)hr.t);      // |p - shadow_vertex.position|
+                A = mk3(ne.ax, ne.ay, ne.az); Bv = mk3(ne.bx, ne.by, ne.bz); Cv = mk3(ne.ex, ne.ey, ne.ez);
+            } else {
+                const HitRec hr = vp.hit[slot];
+                medium = tracked_medium(sc, pp->medium);
+                ray = make_ray(mk3(pp->ox, pp->oy, pp->oz), mk3(pp->dx, pp->dy, pp->dz), sc.eps, INFINITY);
+                t_end = INFINITY; hit_position = mk3(0.0);
+                if (hr.geom >= 0) { hit_position = ray.org + ray.dir * (double)hr.t; t_end = distance(hit_position, ray.org); }
+                A = mk3(1.0); Bv = mk3(1.0); Cv = mk3(1.0);
+            }
+            if (medium != -1) track_begin(sc, sc.media[medium], ray, rng, ts);
+        }
+        if (!__ballot_sync(0xffffffffu, item >= 0)) break;
+        const int stop_below = exhausted ? 1 : refill_below;
+        while (true) {
+            if (item >= 0 && ts.active) {
+                if (NEE) ratio_track_step(sc, sc.media[medium], ray.org, ray.dir, t_end, rng, ts, A, Bv, Cv);
+                else free_flight_step(sc, sc.media[medium], ray, t_end, hit_position, rng, ts, A, Bv, Cv, scatter);
+            }
+            if (__popc(__ballot_sync(0xffffffffu, item >= 0 && ts.active)) < stop_below) break;
+        }
+    }
+}
+
 // ---- stage: main (vol_path_tracing.h:543-760 up to the light sample of the NEE, :311-320) ----
 __global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_upper) {
     const int n = min(n_upper, vp.counts[VQ_MAIN]);
@@ -198,8 +282,14 @@ __global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_u
         d3 thr = mk3(p.tx, p.ty, p.tz), rad = mk3(p.rx, p.ry, p.rz);
         d3 multi = mk3(p.mx, p.my, p.mz);
         bool dead = false;
-        if (p.medium != -1) {
+        if (p.medium != -1 && sc.media[p.medium].kind != LJ_MEDIUM_HETEROGENEOUS) {
             scatter = free_flight(sc, sc.media[p.medium], ray, t_hit, vertex.position, rng, transmittance, trans_dir_pdf, trans_nee_pdf);
+            multi = multi * trans_dir_pdf;
+        } else if (p.medium != -1) {
+            // free-flight sampling was done by k_vol_track<false> (it also advanced p.rng)
+            const VolTrack tr = vp.track[slot];
+            transmittance = mk3(tr.tx, tr.ty, tr.tz); trans_dir_pdf = mk3(tr.dx, tr.dy, tr.dz); trans_nee_pdf = mk3(tr.nx, tr.ny, tr.nz);
+            ray.org = mk3(tr.ox, tr.oy, tr.oz); scatter = tr.scatter != 0;
             multi = multi * trans_dir_pdf;
         } else {
             if (hit) ray.org = vertex.position;
@@ -281,10 +371,8 @@ __global__ void __launch_bounds__(128) k_vol_nee(DScene sc, VolPool vp, int n_up
         const int slot = vp.q_nee[i];
         VolNee ne = vp.nee[slot];
         const HitRec hr = vp.nee_hit[slot];
-        VolPath *pp = &vp.path[slot];
-        VolPath p;                           // only rng / sample / bounces are needed here
-        p.rng = pp->rng; p.sample = pp->sample; p.bounces = pp->bounces;
-        Pcg32 rng = vol_rng(vp, slot, p);
+        VolPath p;                           // only the bounce count is needed here
+        p.bounces = vp.path[slot].bounces;
         d3 pos = mk3(ne.px, ne.py, ne.pz);
         const d3 dir_light = mk3(ne.lx, ne.ly, ne.lz), p_prime = mk3(ne.qx, ne.qy, ne.qz);
         const double eps = sc.eps;
@@ -299,12 +387,17 @@ __global__ void __launch_bounds__(128) k_vol_nee(DScene sc, VolPool vp, int n_up
             next_t = distance(pos, sv.position);
         }
         __syncwarp(together);
-        d3 T = mk3(ne.ax, ne.ay, ne.az), ptn = mk3(ne.bx, ne.by, ne.bz), ptd = mk3(ne.ex, ne.ey, ne.ez);
-        if (ne.shadow_medium != -1)
+        // grid media: the ratio tracking of this segment was done by k_vol_track<true> (ne.a/b/e and the rng are up to date)
+        if (ne.shadow_medium != -1 && sc.media[ne.shadow_medium].kind != LJ_MEDIUM_HETEROGENEOUS) {
+            VolPath *pp = &vp.path[slot];
+            p.rng = pp->rng; p.sample = pp->sample;
+            Pcg32 rng = vol_rng(vp, slot, p);
+            d3 T = mk3(ne.ax, ne.ay, ne.az), ptn = mk3(ne.bx, ne.by, ne.bz), ptd = mk3(ne.ex, ne.ey, ne.ez);
             ratio_track_segment(sc, sc.media[ne.shadow_medium], shadow_ray, pos, dir_light, next_t, rng, T, ptn, ptd);
+            ne.ax = T.x; ne.ay = T.y; ne.az = T.z; ne.bx = ptn.x; ne.by = ptn.y; ne.bz = ptn.z; ne.ex = ptd.x; ne.ey = ptd.y; ne.ez = ptd.z;
+            pp->rng = rng.state;
+        }
         __syncwarp(together);
-        ne.ax = T.x; ne.ay = T.y; ne.az = T.z; ne.bx = ptn.x; ne.by = ptn.y; ne.bz = ptn.z; ne.ex = ptd.x; ne.ey = ptd.y; ne.ez = ptd.z;
-        pp->rng = rng.state;
         bool done = false;
         if (!hit) done = true;
         else if (sv.material_id >= 0) { ne.blocked = 1; done = true; }
@@ -436,7 +529,7 @@ __global__ void k_vol_reset(int *counts, int a, int b) {
 }
 __global__ void k_vol_reset_stage_queues(int *counts) {
     if (threadIdx.x < VQ_COUNT - VQ_MAIN) counts[VQ_MAIN + threadIdx.x] = 0;
-    if (threadIdx.x == 0) counts[VW_EXT] = 0;
+    if (threadIdx.x == 0) { counts[VW_EXT] = 0; counts[VW_TRACK_MAIN] = 0; counts[VW_TRACK_NEE] = 0; }
 }
 __global__ void k_vol_init(VolPool vp, int s_begin) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < vp.capacity; i += (long long)gridDim.x * blockDim.x) {
@@ -472,6 +565,7 @@ static int ensure_vol_pool(lj_scene *s, int capacity, int K, long long npix, Vol
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_path = take(cap * sizeof(VolPath)), o_nee = take(cap * sizeof(VolNee));
     const size_t o_hit = take(cap * sizeof(HitRec)), o_nhit = take(cap * sizeof(HitRec)), o_acc = take(cap * 3 * sizeof(double));
+    const size_t o_trk = take(cap * sizeof(VolTrack));
     const size_t o_er = take(cap * sizeof(ExtRec)), o_es = take(cap * sizeof(int));
     const size_t o_qr = take(cap * sizeof(int)), o_qm = take(cap * sizeof(int)), o_qn = take(cap * sizeof(int)), o_qfm = take(cap * sizeof(int));
     size_t o_qk[LJ_MAT_KIND_COUNT];
@@ -485,7 +579,7 @@ static int ensure_vol_pool(lj_scene *s, int capacity, int K, long long npix, Vol
     }
     char *b = (char *)s->wf_pool;
     vp.capacity = capacity; vp.K = K; vp.npix = npix;
-    vp.path = (VolPath *)(b + o_path); vp.nee = (VolNee *)(b + o_nee); vp.hit = (HitRec *)(b + o_hit); vp.nee_hit = (HitRec *)(b + o_nhit);
+    vp.path = (VolPath *)(b + o_path); vp.nee = (VolNee *)(b + o_nee); vp.hit = (HitRec *)(b + o_hit); vp.nee_hit = (HitRec *)(b + o_nhit); vp.track = (VolTrack *)(b + o_trk);
     vp.accum = (double *)(b + o_acc); vp.ext_ray = (ExtRec *)(b + o_er); vp.ext_slot = (int *)(b + o_es);
     vp.q_regen = (int *)(b + o_qr); vp.q_main = (int *)(b + o_qm); vp.q_nee = (int *)(b + o_qn); vp.q_fin_medium = (int *)(b + o_qfm);
     for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) vp.q_fin_kind[k] = (int *)(b + o_qk[k]);
@@ -513,8 +607,15 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         if (d.num_materials) LJ_CUDA(cudaMemcpy(mats.data(), d.materials, sizeof(lj_material) * d.num_materials, cudaMemcpyDeviceToHost));
         for (const lj_material &m : mats) if (m.kind >= 0 && m.kind < LJ_MAT_KIND_COUNT) kind_present[m.kind] = true;
     }
+    bool grid_media = false;            // any heterogeneous medium -> run the tracking kernels
+    {
+        std::vector<lj_medium> media(d.num_media);
+        if (d.num_media) LJ_CUDA(cudaMemcpy(media.data(), d.media, sizeof(lj_medium) * d.num_media, cudaMemcpyDeviceToHost));
+        for (const lj_medium &m : media) grid_media = grid_media || m.kind == LJ_MEDIUM_HETEROGENEOUS;
+    }
     auto env_int = [](const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; };
     TraceTuning tune; tune.refill_below = env_int("LJ_REFILL_BELOW", 24); tune.prim_thresh = env_int("LJ_PRIM_THRESH", 8);
+    const int track_refill = env_int("LJ_TRACK_REFILL_BELOW", 24);
     const int sm = s->ctx->sm_count;
     const int trace_grid_cap = sm * 16, stage_grid_cap = sm * 16;
     const bool counting = (rl.p.flags & 1) != 0;
@@ -543,6 +644,10 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         else k_vol_extend<false><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, trav, tune);
         k_vol_reset<<<1, 32>>>(vp.counts, VQ_EXT, -1);
         if (stage_timing) cudaEventRecord(ev[2]);
+        if (grid_media) {
+            k_vol_track<false><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, track_refill);
+            k_vol_track<true><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, track_refill);
+        }
         k_vol_main<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
         k_vol_nee<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
         k_vol_finish_medium<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
@@ -558,7 +663,7 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         if (stage_timing) cudaEventRecord(ev[3]);
         LJ_CUDA(cudaMemcpy(h_counts, vp.counts, sizeof h_counts, cudaMemcpyDeviceToHost));
         k_vol_reset_stage_queues<<<1, 32>>>(vp.counts);
-        launches += 8;
+        launches += grid_media ? 10 : 8;
         for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
         const int traced = h_counts[VQ_MAIN] + h_counts[VQ_NEE];
         // the generate stage pushed n_regen' <= n_regen primaries this iteration: traced - n_ext of them
