@@ -28,12 +28,27 @@ extern "C" int lj_init(int device_id, lj_ctx **out) {
     if (device_id < 0 || device_id >= n) { lj_set_error("lj_init: device %d out of range [0,%d)", device_id, n); return LJ_EINVAL; }
     LJ_CUDA(cudaSetDevice(device_id));
     lj_ctx *c = new lj_ctx();
-    c->device = device_id;
+    c->device = device_id; c->wf_pool = nullptr; c->wf_pool_bytes = 0;
     LJ_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device_id));
     *out = c;
     return LJ_OK;
 }
-extern "C" void lj_shutdown(lj_ctx *ctx) { delete ctx; }
+extern "C" void lj_shutdown(lj_ctx *ctx) {
+    if (!ctx) return;
+    if (ctx->wf_pool) { cudaSetDevice(ctx->device); cudaFree(ctx->wf_pool); }
+    delete ctx;
+}
+
+int lj_ctx_arena(lj_ctx *ctx, size_t bytes, void **out) {
+    if (bytes > ctx->wf_pool_bytes) {
+        if (ctx->wf_pool) cudaFree(ctx->wf_pool);
+        ctx->wf_pool = nullptr; ctx->wf_pool_bytes = 0;
+        LJ_CUDA(cudaMalloc(&ctx->wf_pool, bytes));
+        ctx->wf_pool_bytes = bytes;
+    }
+    *out = ctx->wf_pool;
+    return LJ_OK;
+}
 
 template <typename T>
 static int upload(lj_scene *s, const T *host, size_t count, const T **dev) {
@@ -74,7 +89,7 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
     if (rc) return rc;
     LJ_CUDA(cudaSetDevice(ctx->device));
     lj_scene *s = new lj_scene();
-    s->ctx = ctx; s->wf_pool = nullptr; s->wf_pool_bytes = 0; s->wf_capacity = 0;
+    s->ctx = ctx;
     memset(&s->build_stats, 0, sizeof s->build_stats);
     memset(&s->bvh, 0, sizeof s->bvh);
     DScene &d = s->d;
@@ -142,7 +157,6 @@ extern "C" void lj_scene_destroy(lj_scene *s) {
     if (!s) return;
     for (void *p : s->allocs) cudaFree(p);
     lj_bvh_free(s->bvh);
-    if (s->wf_pool) cudaFree(s->wf_pool);
     delete s;
 }
 

@@ -10,7 +10,11 @@ void lj_set_error(const char *fmt, ...);
 struct lj_ctx {
     int device;
     int sm_count;
+    // wavefront path-slot arena: grown on demand, shared by every scene of the context (renders are
+    // synchronous and the ABI is single-threaded per context), freed by lj_shutdown
+    void *wf_pool; size_t wf_pool_bytes;
 };
+int lj_ctx_arena(lj_ctx *ctx, size_t bytes, void **out);
 
 struct lj_scene {
     lj_ctx *ctx;
@@ -18,8 +22,6 @@ struct lj_scene {
     std::vector<void *> allocs;     // every cudaMalloc owned by the scene
     BvhBuildOutput bvh;
     lj_stats build_stats;
-    // wavefront pool (lazily sized, reused across renders)
-    void *wf_pool; size_t wf_pool_bytes; int wf_capacity;
 };
 
 struct RenderLaunch {

@@ -19,11 +19,17 @@
 #include "lj_wave_common.cuh"
 #include <cstdio>
 #include <cstdlib>
+#include <algorithm>
 
 namespace {
 
 enum { VQ_EXT = 0, VQ_REGEN = 1, VQ_MAIN = 2, VQ_NEE = 3, VQ_FIN_MEDIUM = 4, VQ_FIN_KIND0 = 5,
-       VQ_COUNT = VQ_FIN_KIND0 + LJ_MAT_KIND_COUNT, VW_EXT = 24, VW_TRACK_MAIN = 25, VW_TRACK_NEE = 26 };
+       VQ_COUNT = VQ_FIN_KIND0 + LJ_MAT_KIND_COUNT,
+       // grid media: segments whose tracking is complete (input of the main / nee stages), and the two
+       // ping-pong queues of segments suspended at the step budget
+       VT_MAIN_READY = VQ_COUNT, VT_NEE_READY, VT_CONT_MAIN0, VT_CONT_MAIN1, VT_CONT_NEE0, VT_CONT_NEE1, VT_END,
+       VW_EXT = 24, VW_TRACK_MAIN = 25, VW_TRACK_NEE = 26 };
+static_assert(VT_END <= VW_EXT, "queue counters overlap the work counters");
 constexpr int NEE_RAY = (int)0x80000000;    // flag in ext_slot: the ray is an NEE segment
 
 // Per-slot path state that survives between stages (f64, as the reference computes in double).
@@ -52,8 +58,9 @@ struct __align__(16) VolTrack {
     double tx, ty, tz, ox;                  // transmittance, new ray.org.x
     double dx, dy, dz, oy;                  // trans_dir_pdf, new ray.org.y
     double nx, ny, nz, oz;                  // trans_nee_pdf, new ray.org.z
-    int scatter, pad0, pad1, pad2;
-};                                          // 112 B
+    double mjx, mjy, mjz, accum_t;          // suspended segment: majorant along the ray, distance covered
+    int scatter, channel, iteration, pad0;  // suspended segment: sampled channel, collisions so far
+};                                          // 144 B
 
 struct VolPool {
     int capacity, K;
@@ -62,6 +69,7 @@ struct VolPool {
     double *accum;
     ExtRec *ext_ray; int *ext_slot;
     int *q_regen, *q_main, *q_nee, *q_fin_medium, *q_fin_kind[LJ_MAT_KIND_COUNT];
+    int *q_main_ready, *q_nee_ready, *q_cont_main[2], *q_cont_nee[2];
     int *counts;
 };
 
@@ -86,7 +94,8 @@ LJ_D Ray vol_main_ray(const DScene &sc, const VolPath &p) {
 }
 
 // ---- stage: generate (vol_path_tracing.h:509-532) ----
-__global__ void __launch_bounds__(128) k_vol_generate(DScene sc, VolPool vp, int n_regen, int s_end, int ntx, int tile_rank, int tile_world) {
+__global__ void __launch_bounds__(128) k_vol_generate(DScene sc, VolPool vp, int n_upper, int s_end, int ntx, int tile_rank, int tile_world) {
+    const int n_regen = min(n_upper, vp.counts[VQ_REGEN]);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_regen; i += gridDim.x * blockDim.x) {
         const int slot = vp.q_regen[i];
         VolPath p = vp.path[slot];
@@ -193,10 +202,20 @@ LJ_D int tracked_medium(const DScene &sc, int medium) {
 }
 
 template <bool NEE>
-__global__ void __launch_bounds__(128) k_vol_track(DScene sc, VolPool vp, int n_upper, int refill_below) {
-    const int n = min(n_upper, vp.counts[NEE ? VQ_NEE : VQ_MAIN]);
-    const int *queue = NEE ? vp.q_nee : vp.q_main;
-    int item = -1, slot = -1, medium = -1; bool exhausted = false;     // medium = -1: nothing to track for this item
+__global__ void __launch_bounds__(128) k_vol_track(DScene sc, VolPool vp, int n_upper, int refill_below, int budget, int min_items, int parity) {
+    // work = the segments suspended by the previous launch, then the fresh ones from the extend stage
+    const int *q_cont = NEE ? vp.q_cont_nee[parity] : vp.q_cont_main[parity];
+    int *q_susp = NEE ? vp.q_cont_nee[parity ^ 1] : vp.q_cont_main[parity ^ 1];
+    const int c_susp = (NEE ? VT_CONT_NEE0 : VT_CONT_MAIN0) + (parity ^ 1);
+    const int n_cont = min(n_upper, vp.counts[(NEE ? VT_CONT_NEE0 : VT_CONT_MAIN0) + parity]);
+    const int n = min(n_upper, n_cont + vp.counts[NEE ? VQ_NEE : VQ_MAIN]);
+    const int *q_fresh = NEE ? vp.q_nee : vp.q_main;
+    // A segment is suspended (and resumed by the next launch) only once the queue has run dry and it has done
+    // `budget` more steps: while there is work to refill with, long segments cost nothing; afterwards they would
+    // hold the whole iteration back.  With few segments in total nothing else could run anyway: no suspension.
+    if (n < min_items) budget = 0x7fffffff;
+    int *q_ready = NEE ? vp.q_nee_ready : vp.q_main_ready;
+    int item = -1, slot = -1, medium = -1, steps = 0; bool exhausted = false;     // medium = -1: nothing to track for this item
     TrackState ts; ts.active = false;
     Pcg32 rng; rng.state = 0; rng.inc = 1;
     Ray ray = make_ray(mk3(0.0), mk3(0.0), 0, 0);       // main ray, or the shadow segment
@@ -204,27 +223,34 @@ __global__ void __launch_bounds__(128) k_vol_track(DScene sc, VolPool vp, int n_
     d3 A = mk3(1.0), Bv = mk3(1.0), Cv = mk3(1.0);      // main: transmittance, dir pdf, nee pdf; NEE: T_light, p_trans_nee, p_trans_dir
     bool scatter = false;
     while (true) {
-        if (item >= 0 && !ts.active) {                  // retire
+        const bool running = item >= 0 && ts.active && steps < budget;
+        if (item >= 0 && !running) {                    // retire: finished -> ready queue, out of budget -> suspended queue
             if (medium != -1) {
+                VolTrack tr;
                 if (NEE) {
                     VolNee *ne = &vp.nee[slot];
                     ne->ax = A.x; ne->ay = A.y; ne->az = A.z; ne->bx = Bv.x; ne->by = Bv.y; ne->bz = Bv.z; ne->ex = Cv.x; ne->ey = Cv.y; ne->ez = Cv.z;
+                    tr.tx = tr.ty = tr.tz = tr.dx = tr.dy = tr.dz = tr.nx = tr.ny = tr.nz = 0; tr.ox = tr.oy = tr.oz = 0;
                 } else {
-                    VolTrack tr;
                     tr.tx = A.x; tr.ty = A.y; tr.tz = A.z; tr.dx = Bv.x; tr.dy = Bv.y; tr.dz = Bv.z; tr.nx = Cv.x; tr.ny = Cv.y; tr.nz = Cv.z;
-                    tr.ox = ray.org.x; tr.oy = ray.org.y; tr.oz = ray.org.z; tr.scatter = scatter ? 1 : 0; tr.pad0 = tr.pad1 = tr.pad2 = 0;
-                    vp.track[slot] = tr;
+                    tr.ox = ray.org.x; tr.oy = ray.org.y; tr.oz = ray.org.z;
                 }
+                tr.mjx = ts.majorant.x; tr.mjy = ts.majorant.y; tr.mjz = ts.majorant.z; tr.accum_t = ts.accum_t;
+                tr.scatter = scatter ? 1 : 0; tr.channel = ts.channel; tr.iteration = ts.iteration; tr.pad0 = 0;
+                if (!NEE || ts.active) vp.track[slot] = tr;
                 vp.path[slot].rng = rng.state;
             }
+            if (ts.active) q_susp[queue_push_uniform(&vp.counts[c_susp])] = slot;
+            else q_ready[queue_push_uniform(&vp.counts[NEE ? VT_NEE_READY : VT_MAIN_READY])] = slot;
             item = -1;
         }
         if (warp_fetch<false>(&vp.counts[NEE ? VW_TRACK_NEE : VW_TRACK_MAIN], n, item, exhausted)) {
-            slot = queue[item];
+            const bool resumed = item < n_cont;
+            slot = resumed ? q_cont[item] : q_fresh[item - n_cont];
             const VolPath *pp = &vp.path[slot];
             rng.state = pp->rng;
             rng.inc = (((unsigned long long)pp->sample * (unsigned long long)vp.npix + (unsigned long long)(slot % vp.npix)) << 1u) | 1u;
-            scatter = false; ts.active = false;
+            scatter = false; ts.active = false; steps = 0;
             if (NEE) {
                 const VolNee ne = vp.nee[slot];
                 const HitRec hr = vp.nee_hit[slot];
@@ -242,26 +268,32 @@ __global__ void __launch_bounds__(128) k_vol_track(DScene sc, VolPool vp, int n_
                 if (hr.geom >= 0) { hit_position = ray.org + ray.dir * (double)hr.t; t_end = distance(hit_position, ray.org); }
                 A = mk3(1.0); Bv = mk3(1.0); Cv = mk3(1.0);
             }
-            if (medium != -1) track_begin(sc, sc.media[medium], ray, rng, ts);
+            if (resumed) {
+                const VolTrack tr = vp.track[slot];
+                if (!NEE) { A = mk3(tr.tx, tr.ty, tr.tz); Bv = mk3(tr.dx, tr.dy, tr.dz); Cv = mk3(tr.nx, tr.ny, tr.nz); }
+                ts.majorant = mk3(tr.mjx, tr.mjy, tr.mjz); ts.accum_t = tr.accum_t; ts.channel = tr.channel; ts.iteration = tr.iteration;
+                ts.maj_c = comp(ts.majorant, ts.channel); ts.active = true;
+            } else if (medium != -1) track_begin(sc, sc.media[medium], ray, rng, ts);
         }
         if (!__ballot_sync(0xffffffffu, item >= 0)) break;
         const int stop_below = exhausted ? 1 : refill_below;
         while (true) {
-            if (item >= 0 && ts.active) {
+            if (item >= 0 && ts.active && steps < budget) {
                 if (NEE) ratio_track_step(sc, sc.media[medium], ray.org, ray.dir, t_end, rng, ts, A, Bv, Cv);
                 else free_flight_step(sc, sc.media[medium], ray, t_end, hit_position, rng, ts, A, Bv, Cv, scatter);
+                steps += exhausted ? 1 : 0;
             }
-            if (__popc(__ballot_sync(0xffffffffu, item >= 0 && ts.active)) < stop_below) break;
+            if (__popc(__ballot_sync(0xffffffffu, item >= 0 && ts.active && steps < budget)) < stop_below) break;
         }
     }
 }
 
 // ---- stage: main (vol_path_tracing.h:543-760 up to the light sample of the NEE, :311-320) ----
-__global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_upper) {
-    const int n = min(n_upper, vp.counts[VQ_MAIN]);
+__global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_upper, const int *queue, int count_idx) {
+    const int n = min(n_upper, vp.counts[count_idx]);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned together = __activemask();
-        const int slot = vp.q_main[i];
+        const int slot = queue[i];
         VolPath p = vp.path[slot];
         const HitRec hr = vp.hit[slot];
         Pcg32 rng = vol_rng(vp, slot, p);
@@ -364,11 +396,11 @@ __global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_u
 }
 
 // ---- stage: nee = one segment of next_event_estimation_final's loop (:335-439) ----
-__global__ void __launch_bounds__(128) k_vol_nee(DScene sc, VolPool vp, int n_upper) {
-    const int n = min(n_upper, vp.counts[VQ_NEE]);
+__global__ void __launch_bounds__(128) k_vol_nee(DScene sc, VolPool vp, int n_upper, const int *queue, int count_idx) {
+    const int n = min(n_upper, vp.counts[count_idx]);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned together = __activemask();
-        const int slot = vp.q_nee[i];
+        const int slot = queue[i];
         VolNee ne = vp.nee[slot];
         const HitRec hr = vp.nee_hit[slot];
         VolPath p;                           // only the bounce count is needed here
@@ -527,9 +559,13 @@ __global__ void __launch_bounds__(128, LJ_VOL_FINISH_MIN_BLOCKS) k_vol_finish_su
 __global__ void k_vol_reset(int *counts, int a, int b) {
     if (threadIdx.x == 0) { if (a >= 0) counts[a] = 0; if (b >= 0) counts[b] = 0; }
 }
-__global__ void k_vol_reset_stage_queues(int *counts) {
+__global__ void k_vol_reset_stage_queues(int *counts, int parity) {
     if (threadIdx.x < VQ_COUNT - VQ_MAIN) counts[VQ_MAIN + threadIdx.x] = 0;
-    if (threadIdx.x == 0) { counts[VW_EXT] = 0; counts[VW_TRACK_MAIN] = 0; counts[VW_TRACK_NEE] = 0; }
+    if (threadIdx.x == 0) {
+        counts[VW_EXT] = 0; counts[VW_TRACK_MAIN] = 0; counts[VW_TRACK_NEE] = 0;
+        counts[VT_MAIN_READY] = 0; counts[VT_NEE_READY] = 0;
+        counts[VT_CONT_MAIN0 + parity] = 0; counts[VT_CONT_NEE0 + parity] = 0;     // consumed by this iteration
+    }
 }
 __global__ void k_vol_init(VolPool vp, int s_begin) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < vp.capacity; i += (long long)gridDim.x * blockDim.x) {
@@ -540,6 +576,7 @@ __global__ void k_vol_init(VolPool vp, int s_begin) {
         vp.accum[3 * i] = 0; vp.accum[3 * i + 1] = 0; vp.accum[3 * i + 2] = 0;
         vp.q_regen[i] = (int)i;
     }
+    if (blockIdx.x == 0 && threadIdx.x == 0) vp.counts[VQ_REGEN] = vp.capacity;
 }
 __global__ void k_vol_sum(long long npix, int K, const double *accum, double *sum) {
     const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
@@ -570,19 +607,20 @@ static int ensure_vol_pool(lj_scene *s, int capacity, int K, long long npix, Vol
     const size_t o_qr = take(cap * sizeof(int)), o_qm = take(cap * sizeof(int)), o_qn = take(cap * sizeof(int)), o_qfm = take(cap * sizeof(int));
     size_t o_qk[LJ_MAT_KIND_COUNT];
     for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) o_qk[k] = take(cap * sizeof(int));
+    size_t o_tq[6];
+    for (int k = 0; k < 6; k++) o_tq[k] = take(cap * sizeof(int));
     const size_t o_cnt = take(64 * sizeof(int));
-    if (off > s->wf_pool_bytes) {
-        if (s->wf_pool) cudaFree(s->wf_pool);
-        s->wf_pool = nullptr; s->wf_pool_bytes = 0;
-        LJ_CUDA(cudaMalloc(&s->wf_pool, off));
-        s->wf_pool_bytes = off;
-    }
-    char *b = (char *)s->wf_pool;
+    void *arena = nullptr;
+    if (int rc = lj_ctx_arena(s->ctx, off, &arena)) return rc;
+    char *b = (char *)arena;
     vp.capacity = capacity; vp.K = K; vp.npix = npix;
     vp.path = (VolPath *)(b + o_path); vp.nee = (VolNee *)(b + o_nee); vp.hit = (HitRec *)(b + o_hit); vp.nee_hit = (HitRec *)(b + o_nhit); vp.track = (VolTrack *)(b + o_trk);
     vp.accum = (double *)(b + o_acc); vp.ext_ray = (ExtRec *)(b + o_er); vp.ext_slot = (int *)(b + o_es);
     vp.q_regen = (int *)(b + o_qr); vp.q_main = (int *)(b + o_qm); vp.q_nee = (int *)(b + o_qn); vp.q_fin_medium = (int *)(b + o_qfm);
     for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) vp.q_fin_kind[k] = (int *)(b + o_qk[k]);
+    vp.q_main_ready = (int *)(b + o_tq[0]); vp.q_nee_ready = (int *)(b + o_tq[1]);
+    vp.q_cont_main[0] = (int *)(b + o_tq[2]); vp.q_cont_main[1] = (int *)(b + o_tq[3]);
+    vp.q_cont_nee[0] = (int *)(b + o_tq[4]); vp.q_cont_nee[1] = (int *)(b + o_tq[5]);
     vp.counts = (int *)(b + o_cnt);
     return LJ_OK;
 }
@@ -591,7 +629,15 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     const DScene &d = s->d;
     const long long npix = (long long)rl.width * rl.height;
     const int nsamp = rl.s_end - rl.s_begin;
-    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (1LL << 20);
+    bool grid_media = false;            // any heterogeneous medium -> run the tracking kernels
+    {
+        std::vector<lj_medium> media(d.num_media);
+        if (d.num_media) LJ_CUDA(cudaMemcpy(media.data(), d.media, sizeof(lj_medium) * d.num_media, cudaMemcpyDeviceToHost));
+        for (const lj_medium &m : media) grid_media = grid_media || m.kind == LJ_MEDIUM_HETEROGENEOUS;
+    }
+    // slots in flight: grid media want many (the iteration count, not the arithmetic, bounds them: each iteration
+    // waits for its slowest tracking chain), homogeneous scenes run best when the records stay close to L2 size
+    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (grid_media ? (4LL << 20) : (1LL << 20));
     int K = (int)((target + npix - 1) / npix);
     if (K > nsamp) K = nsamp;
     if (K < 1) K = 1;
@@ -607,15 +653,11 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         if (d.num_materials) LJ_CUDA(cudaMemcpy(mats.data(), d.materials, sizeof(lj_material) * d.num_materials, cudaMemcpyDeviceToHost));
         for (const lj_material &m : mats) if (m.kind >= 0 && m.kind < LJ_MAT_KIND_COUNT) kind_present[m.kind] = true;
     }
-    bool grid_media = false;            // any heterogeneous medium -> run the tracking kernels
-    {
-        std::vector<lj_medium> media(d.num_media);
-        if (d.num_media) LJ_CUDA(cudaMemcpy(media.data(), d.media, sizeof(lj_medium) * d.num_media, cudaMemcpyDeviceToHost));
-        for (const lj_medium &m : media) grid_media = grid_media || m.kind == LJ_MEDIUM_HETEROGENEOUS;
-    }
     auto env_int = [](const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; };
     TraceTuning tune; tune.refill_below = env_int("LJ_REFILL_BELOW", 24); tune.prim_thresh = env_int("LJ_PRIM_THRESH", 8);
     const int track_refill = env_int("LJ_TRACK_REFILL_BELOW", 24);
+    const int track_budget = std::max(1, env_int("LJ_TRACK_BUDGET", 16));     // collision steps a segment may take after the queue ran dry
+    const int track_min_items = env_int("LJ_TRACK_MIN_ITEMS", 2048);
     const int sm = s->ctx->sm_count;
     const int trace_grid_cap = sm * 16, stage_grid_cap = sm * 16;
     const bool counting = (rl.p.flags & 1) != 0;
@@ -627,58 +669,96 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     LJ_CUDA(cudaMemsetAsync(vp.counts, 0, 64 * sizeof(int)));
     k_vol_init<<<sm * 8, 256>>>(vp, rl.s_begin);
     LJ_CUDA(cudaGetLastError());
-    int n_regen = capacity, n_ext = 0;
+    // Queue sizes live on the device and every kernel clamps its range to them, so the host does not have to
+    // know them to launch the next iteration: it sizes grids from the last sizes it has seen (or the pool
+    // capacity) and reads the counts back through a ring of pinned buffers, `depth` iterations behind.  The
+    // iterations launched after the one that emptied the pool find empty queues and do nothing.
+    const int depth = stage_timing ? 1 : std::max(1, std::min(8, env_int("LJ_WF_PIPELINE", 4)));
+    int *h_ring = nullptr;
+    LJ_CUDA(cudaMallocHost(&h_ring, sizeof(int) * VT_END * depth));
+    cudaEvent_t done[8];
+    for (int i = 0; i < depth; i++) cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
+    int n_regen = capacity, n_ext = 0, n_cont = 0;  // sizes after the last retired iteration (n_cont: suspended segments)
     unsigned long long launches = 2, rays_primary = 0, rays_ext = 0;
-    int h_counts[VQ_COUNT];
+    unsigned long long launched = 0, retired = 0;
     auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
-    while (n_regen > 0 || n_ext > 0) {
+    bool finished = false;
+    int loop_rc = LJ_OK;
+    while (!finished) {
+        const bool exact = launched == retired;     // nothing in flight: the sizes are the true ones
+        const int regen_upper = exact ? n_regen : capacity;
+        const int upper = exact ? n_ext + n_regen : capacity;
         if (stage_timing) cudaEventRecord(ev[0]);
-        if (n_regen > 0) {
-            k_vol_generate<<<grid_for(n_regen, stage_grid_cap), 128>>>(d, vp, n_regen, rl.s_end, rl.ntx, rl.p.tile_rank, rl.p.tile_world);
+        if (regen_upper > 0) {
+            k_vol_generate<<<grid_for(regen_upper, stage_grid_cap), 128>>>(d, vp, regen_upper, rl.s_end, rl.ntx, rl.p.tile_rank, rl.p.tile_world);
             launches++;
         }
         k_vol_reset<<<1, 32>>>(vp.counts, VQ_REGEN, -1);
         if (stage_timing) cudaEventRecord(ev[1]);
-        const int upper = n_ext + n_regen;
         if (counting) k_vol_extend<true><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, trav, tune);
         else k_vol_extend<false><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, trav, tune);
         k_vol_reset<<<1, 32>>>(vp.counts, VQ_EXT, -1);
         if (stage_timing) cudaEventRecord(ev[2]);
+        const int parity = (int)(launched & 1);
+        // with segments suspended from earlier launches more than `upper` slots may be in the tracking queues
+        const int track_upper = exact ? upper + n_cont : capacity;
         if (grid_media) {
-            k_vol_track<false><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, track_refill);
-            k_vol_track<true><<<grid_for(upper, trace_grid_cap), 128>>>(d, vp, upper, track_refill);
+            k_vol_track<false><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
+            k_vol_track<true><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
+            k_vol_main<<<grid_for(track_upper, stage_grid_cap), 128>>>(d, vp, track_upper, vp.q_main_ready, VT_MAIN_READY);
+            k_vol_nee<<<grid_for(track_upper, stage_grid_cap), 128>>>(d, vp, track_upper, vp.q_nee_ready, VT_NEE_READY);
+        } else {
+            k_vol_main<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper, vp.q_main, VQ_MAIN);
+            k_vol_nee<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper, vp.q_nee, VQ_NEE);
         }
-        k_vol_main<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
-        k_vol_nee<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
-        k_vol_finish_medium<<<grid_for(upper, stage_grid_cap), 128>>>(d, vp, upper);
-        if (kind_present[0]) launch_finish<0>(d, vp, upper, stage_grid_cap);
-        if (kind_present[1]) launch_finish<1>(d, vp, upper, stage_grid_cap);
-        if (kind_present[2]) launch_finish<2>(d, vp, upper, stage_grid_cap);
-        if (kind_present[3]) launch_finish<3>(d, vp, upper, stage_grid_cap);
-        if (kind_present[4]) launch_finish<4>(d, vp, upper, stage_grid_cap);
-        if (kind_present[5]) launch_finish<5>(d, vp, upper, stage_grid_cap);
-        if (kind_present[6]) launch_finish<6>(d, vp, upper, stage_grid_cap);
-        if (kind_present[7]) launch_finish<7>(d, vp, upper, stage_grid_cap);
-        if (kind_present[8]) launch_finish<8>(d, vp, upper, stage_grid_cap);
+        k_vol_finish_medium<<<grid_for(track_upper, stage_grid_cap), 128>>>(d, vp, track_upper);
+        if (kind_present[0]) launch_finish<0>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[1]) launch_finish<1>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[2]) launch_finish<2>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[3]) launch_finish<3>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[4]) launch_finish<4>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[5]) launch_finish<5>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[6]) launch_finish<6>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[7]) launch_finish<7>(d, vp, track_upper, stage_grid_cap);
+        if (kind_present[8]) launch_finish<8>(d, vp, track_upper, stage_grid_cap);
         if (stage_timing) cudaEventRecord(ev[3]);
-        LJ_CUDA(cudaMemcpy(h_counts, vp.counts, sizeof h_counts, cudaMemcpyDeviceToHost));
-        k_vol_reset_stage_queues<<<1, 32>>>(vp.counts);
+        const int ring_slot = (int)(launched % depth);
+        cudaMemcpyAsync(h_ring + ring_slot * VT_END, vp.counts, sizeof(int) * VT_END, cudaMemcpyDeviceToHost);
+        cudaEventRecord(done[ring_slot]);
+        k_vol_reset_stage_queues<<<1, 32>>>(vp.counts, parity);
         launches += grid_media ? 10 : 8;
         for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
-        const int traced = h_counts[VQ_MAIN] + h_counts[VQ_NEE];
-        // the generate stage pushed n_regen' <= n_regen primaries this iteration: traced - n_ext of them
-        const int prim_now = traced - n_ext > 0 ? traced - n_ext : 0;
-        rays_primary += prim_now; rays_ext += traced - prim_now;
-        if (stage_timing) {
-            float ms;
-            cudaEventElapsedTime(&ms, ev[0], ev[1]); st->generate_ms += ms;
-            cudaEventElapsedTime(&ms, ev[1], ev[2]); st->extend_ms += ms;
-            cudaEventElapsedTime(&ms, ev[2], ev[3]); st->shade_ms += ms;
+        launched++;
+        // retire what has completed; block only when the ring is full
+        while (retired < launched) {
+            const int rs = (int)(retired % depth);
+            if (launched - retired < (unsigned long long)depth && cudaEventQuery(done[rs]) == cudaErrorNotReady) break;
+            const cudaError_t e = cudaEventSynchronize(done[rs]);
+            if (e != cudaSuccess) { lj_set_error("volumetric wavefront iteration failed: %s", cudaGetErrorString(e)); loop_rc = LJ_ECUDA; finished = true; break; }
+            const int *h_counts = h_ring + rs * VT_END;
+            const int par_out = (int)((retired & 1) ^ 1);       // the queues this iteration suspended segments into
+            const int traced = h_counts[VQ_MAIN] + h_counts[VQ_NEE];
+            // the generate stage pushed n_regen' <= n_regen primaries this iteration: traced - n_ext of them
+            const int prim_now = traced - n_ext > 0 ? traced - n_ext : 0;
+            rays_primary += prim_now; rays_ext += traced - prim_now;
+            if (stage_timing) {
+                float ms;
+                cudaEventElapsedTime(&ms, ev[0], ev[1]); st->generate_ms += ms;
+                cudaEventElapsedTime(&ms, ev[1], ev[2]); st->extend_ms += ms;
+                cudaEventElapsedTime(&ms, ev[2], ev[3]); st->shade_ms += ms;
+            }
+            n_regen = h_counts[VQ_REGEN];
+            n_ext = h_counts[VQ_EXT];
+            n_cont = h_counts[VT_CONT_MAIN0 + par_out] + h_counts[VT_CONT_NEE0 + par_out];
+            st->iterations++;
+            retired++;
+            if (n_regen == 0 && n_ext == 0 && n_cont == 0) { finished = true; break; }
         }
-        n_regen = h_counts[VQ_REGEN];
-        n_ext = h_counts[VQ_EXT];
-        st->iterations++;
     }
+    cudaDeviceSynchronize();            // drains the (empty) iterations still in flight before the ring is freed
+    for (int i = 0; i < depth; i++) cudaEventDestroy(done[i]);
+    cudaFreeHost(h_ring);
+    if (loop_rc != LJ_OK) return loop_rc;
     k_vol_sum<<<(unsigned)((npix * 3 + 255) / 256), 256>>>(npix, K, vp.accum, dev_sum);
     LJ_CUDA(cudaGetLastError());
     if (counting) {

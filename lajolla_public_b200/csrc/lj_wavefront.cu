@@ -401,13 +401,9 @@ static int ensure_pool(lj_scene *s, int capacity, int K, long long npix, WfPool 
     size_t o_qk[LJ_MAT_KIND_COUNT];
     for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) o_qk[k] = take(cap * sizeof(int));
     size_t o_cnt = take(64 * sizeof(int));
-    if (off > s->wf_pool_bytes) {
-        if (s->wf_pool) cudaFree(s->wf_pool);
-        s->wf_pool = nullptr; s->wf_pool_bytes = 0;
-        LJ_CUDA(cudaMalloc(&s->wf_pool, off));
-        s->wf_pool_bytes = off;
-    }
-    char *b = (char *)s->wf_pool;
+    void *arena = nullptr;
+    if (int rc = lj_ctx_arena(s->ctx, off, &arena)) return rc;
+    char *b = (char *)arena;
     wp.capacity = capacity; wp.K = K; wp.npix = npix;
     wp.ray = (RayRec *)(b + o_ray); wp.thr = (ThrRec *)(b + o_thr); wp.rad = (RadRec *)(b + o_rad); wp.hit = (HitRec *)(b + o_hit);
     wp.accum = (double *)(b + o_acc); wp.ext_ray = (ExtRec *)(b + o_er); wp.ext_slot = (int *)(b + o_es);
@@ -423,7 +419,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     const long long npix = (long long)rl.width * rl.height;
     const int nsamp = rl.s_end - rl.s_begin;
     // pool sizing: K slots per pixel, ~2M paths in flight unless the caller says otherwise
-    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (2LL << 20);
+    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (4LL << 20);
     int K = (int)((target + npix - 1) / npix);
     if (K > nsamp) K = nsamp;
     if (K < 1) K = 1;
