@@ -1,6 +1,7 @@
 // C ABI of include/lajolla_gpu.h: context, scene upload + BVH build, render
 // dispatch, batch ray casting, scene blobs.
 #include "lj_internal.h"
+#include "lj_alloc.h"
 #include "lj_traverse8.cuh"
 
 #include <cstdarg>
@@ -29,38 +30,61 @@ extern "C" int lj_init(int device_id, lj_ctx **out) {
     LJ_CUDA(cudaSetDevice(device_id));
     lj_ctx *c = new lj_ctx();
     c->device = device_id; c->wf_pool = nullptr; c->wf_pool_bytes = 0;
+    {   // keep freed blocks in the device's default memory pool (see lj_alloc.h)
+        cudaMemPool_t pool;
+        LJ_CUDA(cudaDeviceGetDefaultMemPool(&pool, device_id));
+        unsigned long long keep = ~0ULL;
+        LJ_CUDA(cudaMemPoolSetAttribute(pool, cudaMemPoolAttrReleaseThreshold, &keep));
+    }
     LJ_CUDA(cudaDeviceGetAttribute(&c->sm_count, cudaDevAttrMultiProcessorCount, device_id));
     *out = c;
     return LJ_OK;
 }
 extern "C" void lj_shutdown(lj_ctx *ctx) {
     if (!ctx) return;
-    if (ctx->wf_pool) { cudaSetDevice(ctx->device); cudaFree(ctx->wf_pool); }
+    cudaSetDevice(ctx->device);
+    if (ctx->wf_pool) lj_free(ctx->wf_pool);
+    cudaDeviceSynchronize();
+    cudaMemPool_t pool;
+    if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);   // hand the cached blocks back
     delete ctx;
 }
 
 int lj_ctx_arena(lj_ctx *ctx, size_t bytes, void **out) {
     if (bytes > ctx->wf_pool_bytes) {
-        if (ctx->wf_pool) cudaFree(ctx->wf_pool);
+        if (ctx->wf_pool) lj_free(ctx->wf_pool);
         ctx->wf_pool = nullptr; ctx->wf_pool_bytes = 0;
-        LJ_CUDA(cudaMalloc(&ctx->wf_pool, bytes));
+        LJ_CUDA(lj_malloc(&ctx->wf_pool, bytes));
         ctx->wf_pool_bytes = bytes;
     }
     *out = ctx->wf_pool;
     return LJ_OK;
 }
 
-template <typename T>
-static int upload(lj_scene *s, const T *host, size_t count, const T **dev) {
-    *dev = nullptr;
-    size_t bytes = sizeof(T) * (count ? count : 1);
-    void *p = nullptr;
-    LJ_CUDA(cudaMalloc(&p, bytes));
-    s->allocs.push_back(p);
-    if (count) LJ_CUDA(cudaMemcpy(p, host, sizeof(T) * count, cudaMemcpyHostToDevice));
-    *dev = (const T *)p;
-    return LJ_OK;
-}
+// All scene arrays go into ONE device allocation (sub-allocated at 256-byte boundaries) filled with
+// asynchronous copies: a scene is ~20 arrays, and a cudaMalloc + blocking copy per array cost more than
+// the transfer itself (sponza: 73 MB).
+struct Uploader {
+    struct Item { const void *host; size_t bytes, offset; const void **dev; };
+    std::vector<Item> items;
+    size_t total = 0;
+    template <typename T>
+    void add(const T *host, size_t count, const T **dev) {
+        Item it; it.host = host; it.bytes = sizeof(T) * count; it.offset = total; it.dev = (const void **)dev;
+        total += (sizeof(T) * (count ? count : 1) + 255) & ~(size_t)255;
+        items.push_back(it);
+    }
+    int commit(lj_scene *s) {
+        void *base = nullptr;
+        LJ_CUDA(lj_malloc(&base, total ? total : 256));
+        s->allocs.push_back(base);
+        for (const Item &it : items) {
+            *it.dev = (const char *)base + it.offset;
+            if (it.bytes) LJ_CUDA(cudaMemcpyAsync((char *)base + it.offset, it.host, it.bytes, cudaMemcpyHostToDevice));
+        }
+        return LJ_OK;
+    }
+};
 
 static int validate_desc(const lj_scene_desc *d) {
     if (d->camera.width <= 0 || d->camera.height <= 0) { lj_set_error("scene: bad resolution %dx%d", d->camera.width, d->camera.height); return LJ_EINVAL; }
@@ -103,14 +127,13 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
     d.eps = e < 0.01 ? e : 0.01;
     d.envmap_light_id = desc->envmap_light_id;
     d.num_lights = (int)desc->num_lights; d.num_shapes = (int)desc->num_shapes; d.num_materials = (int)desc->num_materials; d.num_media = (int)desc->num_media;
-#define UP(field, cnt) if ((rc = upload(s, desc->field, (size_t)(cnt), &d.field)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+    Uploader up;
+#define UP(field, cnt) up.add(desc->field, (size_t)(cnt), &d.field);
     UP(shapes, desc->num_shapes) UP(lights, desc->num_lights) UP(materials, desc->num_materials) UP(media, desc->num_media)
     UP(textures, desc->num_textures) UP(images1, desc->num_images1) UP(images3, desc->num_images3)
     UP(positions, desc->num_positions * 3) UP(normals, desc->num_positions * 3) UP(uvs, desc->num_positions * 2)
     UP(indices, desc->num_indices * 3) UP(texels, desc->num_texels) UP(tables, desc->num_tables) UP(grid_data, desc->num_grid_data)
 #undef UP
-    d.light_pmf = d.tables + desc->light_pmf_offset;
-    d.light_cdf = d.tables + desc->light_cdf_offset;
 
     // primitive lists for the BVH builder
     std::vector<int> tri_shape(desc->num_indices, 0);
@@ -125,8 +148,11 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
         }
     }
     const int *d_tri_shape; const SpherePrim *d_spheres;
-    if ((rc = upload(s, tri_shape.data(), tri_shape.size(), &d_tri_shape)) != LJ_OK) { lj_scene_destroy(s); return rc; }
-    if ((rc = upload(s, spheres.data(), spheres.size(), &d_spheres)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+    up.add(tri_shape.data(), tri_shape.size(), &d_tri_shape);
+    up.add(spheres.data(), spheres.size(), &d_spheres);
+    if ((rc = up.commit(s)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+    d.light_pmf = d.tables + desc->light_pmf_offset;
+    d.light_cdf = d.tables + desc->light_cdf_offset;
     cudaEventRecord(e1);
 
     BvhBuildInput bi;
@@ -155,7 +181,7 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
 
 extern "C" void lj_scene_destroy(lj_scene *s) {
     if (!s) return;
-    for (void *p : s->allocs) cudaFree(p);
+    for (void *p : s->allocs) lj_free(p);
     lj_bvh_free(s->bvh);
     delete s;
 }
@@ -230,8 +256,8 @@ extern "C" int lj_render(lj_scene *s, const lj_render_params *params, float *rgb
     LJ_CUDA(cudaSetDevice(s->ctx->device));
     int npix = s->d.camera.width * s->d.camera.height;
     double *sum = nullptr; float *rgb = nullptr;
-    LJ_CUDA(cudaMalloc(&sum, sizeof(double) * 3 * (size_t)npix));
-    LJ_CUDA(cudaMalloc(&rgb, sizeof(float) * 3 * (size_t)npix));
+    LJ_CUDA(lj_malloc(&sum, sizeof(double) * 3 * (size_t)npix));
+    LJ_CUDA(lj_malloc(&rgb, sizeof(float) * 3 * (size_t)npix));
     int rc = lj_render_device(s, params, sum, stats);
     if (rc == LJ_OK) {
         RenderLaunch rl; make_launch(s, params, rl);
@@ -241,7 +267,7 @@ extern "C" int lj_render(lj_scene *s, const lj_render_params *params, float *rgb
         cudaError_t e = cudaMemcpy(rgb_out, rgb, sizeof(float) * 3 * (size_t)npix, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { lj_set_error("lj_render: D2H failed: %s", cudaGetErrorString(e)); rc = LJ_ECUDA; }
     }
-    cudaFree(sum); cudaFree(rgb);
+    lj_free(sum); lj_free(rgb);
     return rc;
 }
 
@@ -270,12 +296,12 @@ extern "C" int lj_intersect_batch(lj_scene *s, const lj_ray *rays, int64_t n, lj
     if (n <= 0) return LJ_OK;
     LJ_CUDA(cudaSetDevice(s->ctx->device));
     lj_ray *dr = nullptr; lj_hit *dh = nullptr;
-    LJ_CUDA(cudaMalloc(&dr, sizeof(lj_ray) * n));
-    LJ_CUDA(cudaMalloc(&dh, sizeof(lj_hit) * n));
+    LJ_CUDA(lj_malloc(&dr, sizeof(lj_ray) * n));
+    LJ_CUDA(lj_malloc(&dh, sizeof(lj_hit) * n));
     cudaMemcpy(dr, rays, sizeof(lj_ray) * n, cudaMemcpyHostToDevice);
     k_intersect_batch<<<(unsigned)((n + 127) / 128), 128>>>(s->d, dr, n, dh, any_hit);
     cudaError_t e = cudaMemcpy(hits, dh, sizeof(lj_hit) * n, cudaMemcpyDeviceToHost);
-    cudaFree(dr); cudaFree(dh);
+    lj_free(dr); lj_free(dh);
     if (e != cudaSuccess) { lj_set_error("lj_intersect_batch: %s", cudaGetErrorString(e)); return LJ_ECUDA; }
     return LJ_OK;
 }

@@ -5,6 +5,7 @@
 // assigns them to octant-ordered slots, allocates its inner children / primitive
 // ranges with atomics and quantises the child boxes conservatively.
 #include "lj_bvh_build.h"
+#include "lj_alloc.h"
 
 #include <cfloat>
 #include <cstdio>
@@ -173,10 +174,10 @@ int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left,
     if (n <= 0) return 0;
     int *counters = nullptr;
     Work *q0 = nullptr, *q1 = nullptr;
-    CK(cudaMalloc(&counters, 4 * sizeof(int)));
-    CK(cudaMalloc(&q0, sizeof(Work) * (size_t)n)); CK(cudaMalloc(&q1, sizeof(Work) * (size_t)n));
-    CK(cudaMalloc(&out.bvh8, sizeof(Bvh8Node) * (size_t)n));
-    CK(cudaMalloc(&out.tri_verts8, sizeof(float4) * 3 * (size_t)n));
+    CK(lj_malloc(&counters, 4 * sizeof(int)));
+    CK(lj_malloc(&q0, sizeof(Work) * (size_t)n)); CK(lj_malloc(&q1, sizeof(Work) * (size_t)n));
+    CK(lj_malloc(&out.bvh8, sizeof(Bvh8Node) * (size_t)n));
+    CK(lj_malloc(&out.tri_verts8, sizeof(float4) * 3 * (size_t)n));
     int h_counters[4] = {1 /* nodes allocated: root */, 0 /* prims */, 0 /* out items */, 0};
     CK(cudaMemcpy(counters, h_counters, sizeof h_counters, cudaMemcpyHostToDevice));
     Work root; root.node2 = (n >= 2) ? root2 : ~0; root.node8 = 0;
@@ -198,7 +199,7 @@ int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left,
     }
     out.num_bvh8 = h_counters[0];
     out.num_slots8 = h_counters[1];
-    cudaFree(counters); cudaFree(q0); cudaFree(q1);
+    lj_free(counters); lj_free(q0); lj_free(q1);
     if (out.num_slots8 != n) { snprintf(err, 256, "bvh8 collapse lost primitives: %d of %d", out.num_slots8, n); return -1; }
     return 0;
 }

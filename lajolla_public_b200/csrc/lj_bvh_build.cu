@@ -7,6 +7,7 @@
 //   3. binary radix tree (Karras 2012), bottom-up AABB fit
 //   4. collapse to an 8-wide tree and quantise into 80-byte nodes (Ylitie 2017)
 #include "lj_bvh_build.h"
+#include "lj_alloc.h"
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
@@ -387,13 +388,13 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
     float4 *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
     void *tmp = nullptr; size_t tmp_bytes = 0;
     for (int b = 0; b < 2; b++) {
-        CK(cudaMalloc(&cid[b], 4 * (size_t)n)); CK(cudaMalloc(&cc[b], 4 * (size_t)n));
-        CK(cudaMalloc(&clo[b], sizeof(float4) * n)); CK(cudaMalloc(&chi[b], sizeof(float4) * n));
+        CK(lj_malloc(&cid[b], 4 * (size_t)n)); CK(lj_malloc(&cc[b], 4 * (size_t)n));
+        CK(lj_malloc(&clo[b], sizeof(float4) * n)); CK(lj_malloc(&chi[b], sizeof(float4) * n));
     }
-    CK(cudaMalloc(&nn, 4 * (size_t)n)); CK(cudaMalloc(&valid, 4 * (size_t)(n + 1))); CK(cudaMalloc(&pos, 4 * (size_t)(n + 1)));
-    CK(cudaMalloc(&counter, 4)); CK(cudaMemset(counter, 0, 4));
+    CK(lj_malloc(&nn, 4 * (size_t)n)); CK(lj_malloc(&valid, 4 * (size_t)(n + 1))); CK(lj_malloc(&pos, 4 * (size_t)(n + 1)));
+    CK(lj_malloc(&counter, 4)); CK(cudaMemset(counter, 0, 4));
     CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, valid, pos, n + 1));
-    CK(cudaMalloc(&tmp, tmp_bytes));
+    CK(lj_malloc(&tmp, tmp_bytes));
     k_ploc_init<<<(n + 255) / 256, 256>>>(n, vals, prim_lo, prim_hi, cid[0], cc[0], clo[0], chi[0]);
     int m = n, cur = 0, rounds = 0;
     while (m > 1) {
@@ -410,8 +411,8 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
         if (++rounds > 4096) { snprintf(err, 256, "PLOC did not converge"); return -1; }
     }
     CK(cudaMemcpy(root_out, cid[cur], 4, cudaMemcpyDeviceToHost));
-    for (int b = 0; b < 2; b++) { cudaFree(cid[b]); cudaFree(cc[b]); cudaFree(clo[b]); cudaFree(chi[b]); }
-    cudaFree(nn); cudaFree(valid); cudaFree(pos); cudaFree(counter); cudaFree(tmp);
+    for (int b = 0; b < 2; b++) { lj_free(cid[b]); lj_free(cc[b]); lj_free(clo[b]); lj_free(chi[b]); }
+    lj_free(nn); lj_free(valid); lj_free(pos); lj_free(counter); lj_free(tmp);
     return 0;
 }
 
@@ -427,8 +428,8 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
     const int G = (n + B - 1) / B;
     float4 *prim_lo = nullptr, *prim_hi = nullptr;
     float *bounds = nullptr;
-    CK(cudaMalloc(&prim_lo, sizeof(float4) * n)); CK(cudaMalloc(&prim_hi, sizeof(float4) * n));
-    CK(cudaMalloc(&bounds, sizeof(float) * 6));
+    CK(lj_malloc(&prim_lo, sizeof(float4) * n)); CK(lj_malloc(&prim_hi, sizeof(float4) * n));
+    CK(lj_malloc(&bounds, sizeof(float) * 6));
     float init_b[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
     CK(cudaMemcpy(bounds, init_b, sizeof init_b, cudaMemcpyHostToDevice));
     k_prim_bounds<<<G, B>>>(in.num_tris, in.num_spheres, in.positions, in.indices, in.tri_shape, in.shapes, in.spheres, prim_lo, prim_hi, bounds);
@@ -448,10 +449,10 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
         const double scene_area = sx * sy + sy * sz + sz * sx;
         if (alpha > 0 && in.num_tris > 0 && scene_area > 0) {
             int *ref_count = nullptr, *ref_offset = nullptr; void *stmp = nullptr; size_t stmp_bytes = 0;
-            CK(cudaMalloc(&ref_count, 4 * (size_t)(n + 1))); CK(cudaMalloc(&ref_offset, 4 * (size_t)(n + 1)));
+            CK(lj_malloc(&ref_count, 4 * (size_t)(n + 1))); CK(lj_malloc(&ref_offset, 4 * (size_t)(n + 1)));
             CK(cudaMemset(ref_count, 0, 4 * (size_t)(n + 1)));
             CK(cub::DeviceScan::ExclusiveSum(nullptr, stmp_bytes, ref_count, ref_offset, n + 1));
-            CK(cudaMalloc(&stmp, stmp_bytes));
+            CK(lj_malloc(&stmp, stmp_bytes));
             int total = n;
             for (int attempt = 0; attempt < 8; attempt++) {
                 k_split_refs<false><<<G, B>>>(in.num_tris, in.num_spheres, in.positions, in.indices, in.tri_shape, in.shapes, prim_lo, prim_hi,
@@ -464,15 +465,15 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
             }
             if (total > n && (double)total <= 2.0 * n) {
                 float4 *ref_lo = nullptr, *ref_hi = nullptr;
-                CK(cudaMalloc(&ref_lo, sizeof(float4) * (size_t)total)); CK(cudaMalloc(&ref_hi, sizeof(float4) * (size_t)total));
-                CK(cudaMalloc(&ref_prim, 4 * (size_t)total));
+                CK(lj_malloc(&ref_lo, sizeof(float4) * (size_t)total)); CK(lj_malloc(&ref_hi, sizeof(float4) * (size_t)total));
+                CK(lj_malloc(&ref_prim, 4 * (size_t)total));
                 k_split_refs<true><<<G, B>>>(in.num_tris, in.num_spheres, in.positions, in.indices, in.tri_shape, in.shapes, prim_lo, prim_hi,
                                              alpha * scene_area, nullptr, ref_offset, ref_lo, ref_hi, ref_prim);
                 CK(cudaGetLastError());
-                cudaFree(prim_lo); cudaFree(prim_hi);
+                lj_free(prim_lo); lj_free(prim_hi);
                 prim_lo = ref_lo; prim_hi = ref_hi;
             }
-            cudaFree(ref_count); cudaFree(ref_offset); cudaFree(stmp);
+            lj_free(ref_count); lj_free(ref_offset); lj_free(stmp);
             if (ref_prim) return lj_bvh_build_refs(in, out, err, total, prim_lo, prim_hi, ref_prim, bounds);
         }
     }
@@ -490,25 +491,25 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     unsigned long long *keys = nullptr, *keys2 = nullptr;
     int *vals = nullptr, *vals2 = nullptr, *left = nullptr, *right = nullptr, *par_i = nullptr, *par_l = nullptr, *flags = nullptr, *count = nullptr;
     void *tmp = nullptr;
-    CK(cudaMalloc(&keys, 8 * (size_t)n)); CK(cudaMalloc(&keys2, 8 * (size_t)n));
-    CK(cudaMalloc(&vals, 4 * (size_t)n)); CK(cudaMalloc(&vals2, 4 * (size_t)n));
+    CK(lj_malloc(&keys, 8 * (size_t)n)); CK(lj_malloc(&keys2, 8 * (size_t)n));
+    CK(lj_malloc(&vals, 4 * (size_t)n)); CK(lj_malloc(&vals2, 4 * (size_t)n));
     k_morton<<<G, B>>>(n, prim_lo, prim_hi, bounds, keys, vals);
     CK(cudaGetLastError());
     size_t tmp_bytes = 0;
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
-    CK(cudaMalloc(&tmp, tmp_bytes));
+    CK(lj_malloc(&tmp, tmp_bytes));
     CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
 
-    CK(cudaMalloc(&out.tri_verts, sizeof(float4) * 3 * (size_t)n));
+    CK(lj_malloc(&out.tri_verts, sizeof(float4) * 3 * (size_t)n));
     k_emit_prims<<<G, B>>>(n, in.num_tris, vals2, ref_prim, in.positions, in.indices, in.tri_shape, in.shapes, in.spheres, out.tri_verts);
     CK(cudaGetLastError());
 
     if (n >= 2) {
-        CK(cudaMalloc(&left, 4 * (size_t)n)); CK(cudaMalloc(&right, 4 * (size_t)n));
-        CK(cudaMalloc(&par_i, 4 * (size_t)n)); CK(cudaMalloc(&par_l, 4 * (size_t)n));
-        CK(cudaMalloc(&flags, 4 * (size_t)n)); CK(cudaMemset(flags, 0, 4 * (size_t)n));
-        CK(cudaMalloc(&node_lo, sizeof(float4) * n)); CK(cudaMalloc(&node_hi, sizeof(float4) * n));
-        CK(cudaMalloc(&count, 4 * (size_t)n));
+        CK(lj_malloc(&left, 4 * (size_t)n)); CK(lj_malloc(&right, 4 * (size_t)n));
+        CK(lj_malloc(&par_i, 4 * (size_t)n)); CK(lj_malloc(&par_l, 4 * (size_t)n));
+        CK(lj_malloc(&flags, 4 * (size_t)n)); CK(cudaMemset(flags, 0, 4 * (size_t)n));
+        CK(lj_malloc(&node_lo, sizeof(float4) * n)); CK(lj_malloc(&node_hi, sizeof(float4) * n));
+        CK(lj_malloc(&count, 4 * (size_t)n));
         const char *bsel = getenv("LJ_BUILDER");       // "lbvh" keeps the plain radix tree; default PLOC
         if (bsel && bsel[0] == 'l') {
             k_radix_tree<<<G, B>>>(n, keys2, left, right, par_i, par_l);
@@ -520,7 +521,7 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
         } else {
             if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, &out.bvh2_root, err) != 0) return -1;
         }
-        CK(cudaMalloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
+        CK(lj_malloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
         k_emit_bvh2<<<G, B>>>(n, left, right, node_lo, node_hi, out.bvh2);
         CK(cudaGetLastError());
         out.num_bvh2 = n - 1;
@@ -528,13 +529,13 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     CK(cudaDeviceSynchronize());
     // the 8-wide collapse consumes the binary tree (lj_bvh8_build.cu)
     int rc = lj_bvh8_collapse(n, out.bvh2_root, out.tri_verts, left, right, count, node_lo, node_hi, vals2, prim_lo, prim_hi, out, err);
-    cudaFree(ref_prim);
-    cudaFree(prim_lo); cudaFree(prim_hi); cudaFree(bounds); cudaFree(keys); cudaFree(keys2); cudaFree(vals); cudaFree(vals2);
-    cudaFree(left); cudaFree(right); cudaFree(par_i); cudaFree(par_l); cudaFree(flags); cudaFree(node_lo); cudaFree(node_hi); cudaFree(tmp); cudaFree(count);
+    lj_free(ref_prim);
+    lj_free(prim_lo); lj_free(prim_hi); lj_free(bounds); lj_free(keys); lj_free(keys2); lj_free(vals); lj_free(vals2);
+    lj_free(left); lj_free(right); lj_free(par_i); lj_free(par_l); lj_free(flags); lj_free(node_lo); lj_free(node_hi); lj_free(tmp); lj_free(count);
     return rc;
 }
 
 void lj_bvh_free(BvhBuildOutput &out) {
-    cudaFree(out.tri_verts); cudaFree(out.bvh2); cudaFree(out.bvh8); cudaFree(out.tri_verts8);
+    lj_free(out.tri_verts); lj_free(out.bvh2); lj_free(out.bvh8); lj_free(out.tri_verts8);
     memset(&out, 0, sizeof out);
 }

@@ -2,6 +2,7 @@
 // (mode B, one lane per pixel-sample slot) and the primary-ray AOV renderers.
 // The wavefront engine lives in lj_wavefront.cu.
 #include "lj_internal.h"
+#include "lj_alloc.h"
 #include "lj_path.cuh"
 #include "lj_volpath.cuh"
 
@@ -89,7 +90,7 @@ static int finish_counters(unsigned long long *d_counters, lj_stats *st) {
     unsigned long long c[3];
     LJ_CUDA(cudaMemcpy(c, d_counters, sizeof c, cudaMemcpyDeviceToHost));
     st->rays_primary += c[0]; st->rays_extension += c[1]; st->rays_shadow += c[2];
-    cudaFree(d_counters);
+    lj_free(d_counters);
     return LJ_OK;
 }
 
@@ -97,7 +98,7 @@ template <int INTEGRATOR>
 static int run_tiles(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st) {
     size_t npix = (size_t)rl.width * rl.height;
     unsigned long long *d_counters;
-    LJ_CUDA(cudaMalloc(&d_counters, 3 * sizeof(unsigned long long)));
+    LJ_CUDA(lj_malloc(&d_counters, 3 * sizeof(unsigned long long)));
     LJ_CUDA(cudaMemset(d_counters, 0, 3 * sizeof(unsigned long long)));
     LJ_CUDA(cudaMemsetAsync(dev_sum, 0, sizeof(double) * 3 * npix));
     int ntiles = rl.ntx * rl.nty;
@@ -115,9 +116,9 @@ static int run_mega(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_sta
     int nsamp = rl.s_end - rl.s_begin;
     int K = nsamp < 8 ? nsamp : 8;
     unsigned long long *d_counters; double *partial;
-    LJ_CUDA(cudaMalloc(&d_counters, 3 * sizeof(unsigned long long)));
+    LJ_CUDA(lj_malloc(&d_counters, 3 * sizeof(unsigned long long)));
     LJ_CUDA(cudaMemset(d_counters, 0, 3 * sizeof(unsigned long long)));
-    LJ_CUDA(cudaMalloc(&partial, sizeof(double) * 3 * npix * K));
+    LJ_CUDA(lj_malloc(&partial, sizeof(double) * 3 * npix * K));
     long long total = (long long)npix * K;
     k_mega_mode_b<INTEGRATOR><<<(unsigned)((total + 127) / 128), 128>>>(s->d, rl.ntx, rl.s_begin, rl.s_end, K, rl.p.tile_rank, rl.p.tile_world, partial, d_counters);
     LJ_CUDA(cudaGetLastError());
@@ -126,7 +127,7 @@ static int run_mega(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_sta
     st->kernel_launches += 2;
     st->samples = npix * (size_t)nsamp;
     int rc = finish_counters(d_counters, st);
-    cudaFree(partial);
+    lj_free(partial);
     return rc;
 }
 
