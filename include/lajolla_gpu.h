@@ -212,6 +212,33 @@ void lj_scene_desc_free(lj_scene_desc *desc);
 /* page-lock (pin != 0) or unlock the arrays of a loaded desc so uploads run from pinned host memory */
 int lj_scene_desc_pin(lj_scene_desc *desc, int pin);
 
+/* ---- output step: imwrite(), image.cpp:135-173 ----
+ * Encodes an f32 RGB image (rows top to bottom, as lj_render returns it) the way the reference writes it.
+ *   LJ_IMAGE_PFM: "PF\n<w> <h>\n-1\n" + the f32 rows top to bottom (image.cpp:141-149), byte-identical.
+ *   LJ_IMAGE_EXR: scanline OpenEXR, channels B G R as HALF with tinyexr's float_to_half_full rounding
+ *                 (tinyexr.h:889-924, reached through SaveEXR(..., fp16) at image.cpp:161-166); lines are stored
+ *                 uncompressed where the reference deflates 16-line blocks: same decoded pixels.
+ * The conversion and the scanline layout run on the device. */
+enum { LJ_IMAGE_PFM = 0, LJ_IMAGE_EXR = 1 };
+uint64_t lj_image_encoded_size(int32_t format, int32_t width, int32_t height);      /* exact size; 0 = bad arguments */
+int lj_image_encode(lj_ctx *ctx, int32_t format, const float *rgb, int32_t width, int32_t height,
+                    void *out, uint64_t capacity, uint64_t *bytes);
+/* format from the extension (.pfm / .exr) like imwrite; anything else is LJ_EINVAL ("Unsupported image format") */
+int lj_image_write(lj_ctx *ctx, const char *filename, const float *rgb, int32_t width, int32_t height);
+
+/* The same from the f64 radiance sums lj_render_device leaves on the device (sum / spp, render.cpp:94, then
+ * narrowed to f32, image.cpp:146), without a host round trip of the sums; and the progressive-render
+ * checkpoint: the sums plus the sample range [sample_begin, sample_end) they cover, to be resumed with
+ * lj_render_params.sample_begin / sample_end. */
+int lj_accum_finalize(lj_ctx *ctx, const double *dev_sum, int32_t width, int32_t height, int32_t spp, float *rgb_out);
+int lj_accum_encode(lj_ctx *ctx, int32_t format, const double *dev_sum, int32_t width, int32_t height, int32_t spp,
+                    void *out, uint64_t capacity, uint64_t *bytes);
+int lj_accum_write(lj_ctx *ctx, const char *filename, const double *dev_sum, int32_t width, int32_t height, int32_t spp);
+int lj_accum_save(lj_ctx *ctx, const char *filename, const double *dev_sum, int32_t width, int32_t height,
+                  int32_t sample_begin, int32_t sample_end);
+int lj_accum_load(lj_ctx *ctx, const char *filename, double *dev_sum, int32_t width, int32_t height,
+                  int32_t *sample_begin, int32_t *sample_end);
+
 #ifdef __cplusplus
 }
 #endif

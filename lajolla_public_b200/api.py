@@ -67,7 +67,8 @@ HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("geom_id", "<i4
 # every symbol include/lajolla_gpu.h declares
 ABI_SYMBOLS = ["lj_init", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", "lj_render", "lj_render_device",
                "lj_intersect_batch", "lj_scene_info", "lj_last_error", "lj_scene_desc_save", "lj_scene_desc_load",
-               "lj_scene_desc_free", "lj_scene_desc_pin"]
+               "lj_scene_desc_free", "lj_scene_desc_pin", "lj_image_encoded_size", "lj_image_encode", "lj_image_write",
+               "lj_accum_finalize", "lj_accum_encode", "lj_accum_write", "lj_accum_save", "lj_accum_load"]
 
 _lib = None
 
@@ -98,6 +99,15 @@ def load_library():
     lib.lj_scene_desc_free.argtypes = [C.c_void_p]
     lib.lj_scene_desc_free.restype = None
     lib.lj_scene_desc_pin.argtypes = [C.c_void_p, C.c_int]
+    lib.lj_image_encoded_size.argtypes = [C.c_int32, C.c_int32, C.c_int32]
+    lib.lj_image_encoded_size.restype = C.c_uint64
+    lib.lj_image_encode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    lib.lj_image_write.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32]
+    lib.lj_accum_finalize.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    lib.lj_accum_encode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
+    lib.lj_accum_write.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
+    lib.lj_accum_save.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
+    lib.lj_accum_load.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
     _lib = lib
     return lib
 
@@ -122,10 +132,51 @@ class LajollaGPU:
     def scene_from_desc(self, desc):
         return Scene(self, desc=desc)
 
+    # ---- output step (imwrite, image.cpp:135-173) ----
+    def encode_image(self, img, fmt):
+        """f32 (h, w, 3) image -> bytes of the .pfm / .exr file the reference's imwrite would write."""
+        img = np.ascontiguousarray(img, dtype=np.float32)
+        h, w = img.shape[:2]
+        cap = self.lib.lj_image_encoded_size(int(fmt), w, h)
+        buf = (C.c_ubyte * max(int(cap), 1))()
+        n = C.c_uint64()
+        _check(self.lib, self.lib.lj_image_encode(self.handle, int(fmt), img.ctypes.data, w, h, buf, cap, C.byref(n)), "lj_image_encode")
+        return bytes(buf[:n.value])
+
+    def write_image(self, path, img):
+        img = np.ascontiguousarray(img, dtype=np.float32)
+        _check(self.lib, self.lib.lj_image_write(self.handle, os.fsencode(path), img.ctypes.data, img.shape[1], img.shape[0]), "lj_image_write")
+
+    def accum_finalize(self, dev_ptr, w, h, spp):
+        out = np.empty((h, w, 3), dtype=np.float32)
+        _check(self.lib, self.lib.lj_accum_finalize(self.handle, C.c_void_p(dev_ptr), w, h, int(spp), out.ctypes.data), "lj_accum_finalize")
+        return out
+
+    def accum_encode(self, dev_ptr, w, h, spp, fmt):
+        cap = self.lib.lj_image_encoded_size(int(fmt), w, h)
+        buf = (C.c_ubyte * max(int(cap), 1))()
+        n = C.c_uint64()
+        _check(self.lib, self.lib.lj_accum_encode(self.handle, int(fmt), C.c_void_p(dev_ptr), w, h, int(spp), buf, cap, C.byref(n)), "lj_accum_encode")
+        return bytes(buf[:n.value])
+
+    def accum_write(self, path, dev_ptr, w, h, spp):
+        _check(self.lib, self.lib.lj_accum_write(self.handle, os.fsencode(path), C.c_void_p(dev_ptr), w, h, int(spp)), "lj_accum_write")
+
+    def accum_save(self, path, dev_ptr, w, h, sample_begin, sample_end):
+        _check(self.lib, self.lib.lj_accum_save(self.handle, os.fsencode(path), C.c_void_p(dev_ptr), w, h, int(sample_begin), int(sample_end)), "lj_accum_save")
+
+    def accum_load(self, path, dev_ptr, w, h):
+        b, e = C.c_int32(), C.c_int32()
+        _check(self.lib, self.lib.lj_accum_load(self.handle, os.fsencode(path), C.c_void_p(dev_ptr), w, h, C.byref(b), C.byref(e)), "lj_accum_load")
+        return b.value, e.value
+
     def close(self):
         if self.handle:
             self.lib.lj_shutdown(self.handle)
             self.handle = C.c_void_p()
+
+
+IMAGE_PFM, IMAGE_EXR = 0, 1
 
 
 class HostSceneDesc:
@@ -221,3 +272,4 @@ def write_pfm(path, img):
     with open(path, "wb") as f:
         f.write(b"PF\n%d %d\n-1\n" % (img.shape[1], img.shape[0]))
         f.write(img.tobytes())
+

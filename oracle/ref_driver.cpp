@@ -20,6 +20,10 @@
 //       primary-ray closest hits through the reference's intersect() for the
 //       pixel-centre ray of every pixel (aux_render's ray, render.cpp:27):
 //       per pixel {float t,u,v; int geomID, primID} with t = distance.
+//   ref_driver imwrite <in.f32img> <out.pfm|out.exr>
+//       the reference's imwrite() (image.cpp:135-173) applied to a raw image
+//       {int32 w, h; float rgb[h][w][3]} (widened to the Image3 doubles imwrite takes):
+//       the golden generator for the output-encode step.
 //   ref_driver rng <n>
 //       first n next_pcg32_real<double> draws of init_pcg32(7) (known-answer
 //       vector for pcg.h:32-67).
@@ -166,6 +170,20 @@ static int cmd_hits(int argc, char **argv) {
     return 0;
 }
 
+static int cmd_imwrite(int argc, char **argv) {
+    if (argc < 4) { fprintf(stderr, "usage: ref_driver imwrite in.f32img out.pfm|out.exr\n"); return 2; }
+    std::ifstream f(argv[2], std::ios::binary);
+    int w = 0, h = 0;
+    f.read((char *)&w, 4); f.read((char *)&h, 4);
+    if (!f || w <= 0 || h <= 0) { fprintf(stderr, "bad input %s\n", argv[2]); return 2; }
+    std::vector<float> rgb((size_t)w * h * 3);
+    f.read((char *)rgb.data(), rgb.size() * sizeof(float));
+    Image3 img(w, h);
+    for (int i = 0; i < w * h; i++) img(i) = Vector3{rgb[3 * i], rgb[3 * i + 1], rgb[3 * i + 2]};
+    imwrite(argv[3], img);
+    return 0;
+}
+
 static int cmd_rng(int argc, char **argv) {
     int n = argc > 2 ? atoi(argv[2]) : 8;
     pcg32_state rng = init_pcg32(7);
@@ -174,10 +192,11 @@ static int cmd_rng(int argc, char **argv) {
 }
 
 int main(int argc, char **argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|hits|rng ...\n"); return 2; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|hits|imwrite|rng ...\n"); return 2; }
     std::string cmd = argv[1];
     if (cmd == "render") return cmd_render(argc, argv);
     if (cmd == "hits") return cmd_hits(argc, argv);
+    if (cmd == "imwrite") return cmd_imwrite(argc, argv);
     if (cmd == "rng") return cmd_rng(argc, argv);
     fprintf(stderr, "unknown command %s\n", cmd.c_str());
     return 2;

@@ -125,3 +125,30 @@ def test_golden_manifest_is_consistent():
             assert img.shape == (e["res"][1], e["res"][0], 3) and img.dtype == np.float32
             assert abs(float(img.mean()) - meta["mean"]) < 1e-6
             assert np.isfinite(img).all()
+
+
+def test_imwrite_golden_is_the_references_output(tmp_path):
+    """tests/golden/imwrite_kat.{exr,pfm} are what the reference's imwrite() (image.cpp:135-173) writes for
+    imwrite_kat.f32img: re-minted here when the oracle binary is present, and in any case decoded and compared
+    with the numpy restatement of tinyexr's float -> half conversion (tinyexr.h:889-924)."""
+    import struct
+    import subprocess
+    from exr_util import half_bits_tinyexr, read_exr_half
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    raw = open(os.path.join(gold, "imwrite_kat.f32img"), "rb").read()
+    w, h = struct.unpack_from("<ii", raw)
+    img = np.frombuffer(raw, dtype="<f4", offset=8).reshape(h, w, 3)
+    exr = open(os.path.join(gold, "imwrite_kat.exr"), "rb").read()
+    pfm = open(os.path.join(gold, "imwrite_kat.pfm"), "rb").read()
+    ch, attrs = read_exr_half(exr)
+    want = half_bits_tinyexr(img)
+    assert attrs["compression"][1] == b"\x03"            # ZIP, as SaveEXR picks for images >= 16 px
+    for ci, c in enumerate("RGB"):
+        assert np.array_equal(ch[c], want[:, :, ci])
+    assert pfm == b"PF\n%d %d\n-1\n" % (w, h) + img.tobytes()
+    drv = os.path.join(os.path.dirname(gold), "..", "oracle", "_ref", "ref_driver")
+    if os.path.exists(drv):
+        for ext, committed in (("exr", exr), ("pfm", pfm)):
+            out = tmp_path / ("kat." + ext)
+            subprocess.run([drv, "imwrite", os.path.join(gold, "imwrite_kat.f32img"), str(out)], check=True)
+            assert out.read_bytes() == committed

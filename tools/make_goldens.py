@@ -60,8 +60,30 @@ def run(cmd):
     return r.stdout
 
 
+def imwrite_kat():
+    """Known-answer vector for the output step: a small f32 image full of rounding / overflow / denormal /
+    non-finite cases, written by the reference's own imwrite() as .exr (tinyexr, fp16, ZIP) and .pfm."""
+    import struct
+    rng = np.random.default_rng(7)
+    w, h = 37, 21
+    img = rng.standard_normal((h, w, 3)).astype(np.float32) * np.exp(rng.uniform(-20, 12, (h, w, 3))).astype(np.float32)
+    special = np.array([0.0, -0.0, 1.0, -1.0, 65504.0, 65520.0, 65519.99, 1e-8, 5.96e-8, 2.98e-8, 2.9802322e-08, 6.1e-5,
+                        6.0975552e-05, np.inf, -np.inf, np.nan, 1e-40, -1e-40, 1.0009766, 1.00048828125, 1.000488,
+                        0.33333334, 1e5, -1e5, 3.0e-8], dtype=np.float32)
+    img.reshape(-1)[:len(special)] = special
+    gold = os.path.join(ROOT, "tests/golden")
+    src = os.path.join(gold, "imwrite_kat.f32img")
+    with open(src, "wb") as f:
+        f.write(struct.pack("<ii", w, h) + img.tobytes())
+    for ext in ("exr", "pfm"):
+        run([DRIVER, "imwrite", src, os.path.join(gold, "imwrite_kat." + ext)])
+    print(f"  imwrite_kat: {w}x{h} -> .exr {os.path.getsize(os.path.join(gold, 'imwrite_kat.exr'))} B, .pfm {os.path.getsize(os.path.join(gold, 'imwrite_kat.pfm'))} B")
+
+
 def main():
     only = set(sys.argv[1:])
+    if not only or "imwrite_kat" in only:
+        imwrite_kat()
     os.makedirs(os.path.join(ROOT, "scenes_flat"), exist_ok=True)
     manifest_path = os.path.join(ROOT, "tests/golden/manifest.json")
     manifest = json.load(open(manifest_path)) if os.path.exists(manifest_path) else {}
