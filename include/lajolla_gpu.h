@@ -182,6 +182,7 @@ typedef struct lj_stats {
     uint64_t bvh_nodes, bvh_prims;
     uint64_t shadow_nodes_visited, shadow_prims_tested;   /* flags bit0, any-hit rays */
     uint64_t iterations;                  /* wavefront iterations */
+    double tables_build_ms;               /* lj_scene_create_ex with LJ_SCENE_BUILD_TABLES: device time of the scene build step */
 } lj_stats;
 
 typedef struct lj_ray { float org[3], tnear, dir[3], tfar; } lj_ray;           /* RTCRay subset, f32 seam */
@@ -194,6 +195,20 @@ typedef struct lj_scene lj_scene;
 int lj_init(int device_id, lj_ctx **out);                      /* replaces rtcNewDevice + parallel_init (main.cpp:30-31) */
 void lj_shutdown(lj_ctx *ctx);                                 /* main.cpp:47-48 */
 int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene **out);   /* Scene::Scene's Embree build, scene.cpp:20-34 */
+/* Scene build step on the device (scene.cpp:36-52 minus the Embree build).  With
+ * LJ_SCENE_BUILD_TABLES the derived data of `desc` -- mip levels >= 1 (make_mipmap, mipmap.h:25-48), per-mesh
+ * area tables and total_area (triangle_mesh.inl:48-63, table_dist.cpp:3-25), the envmap TableDist2D and
+ * total_values (envmap.inl:75-98, table_dist.cpp:40-114) and the light distribution (scene.cpp:46-51) -- are NOT
+ * read: their ranges in `texels` / `tables` only reserve space, and kernels derive them from the level-0 texels,
+ * positions / indices and light records.  Bit-identical to the host-built values, except that the envmap rows go
+ * through the device's sin().  LJ_SCENE_POISON_DERIVED (tests) overwrites those ranges with NaN first.
+ * lj_scene_create reads LJ_BUILD_TABLES=1 from the environment as the same switch. */
+#define LJ_SCENE_BUILD_TABLES 1u
+#define LJ_SCENE_POISON_DERIVED 2u
+int lj_scene_create_ex(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flags, lj_scene **out);
+/* reads the device copies of the derived arrays back (verification of the step above) */
+int lj_scene_read_derived(lj_scene *scene, double *tables, uint64_t num_tables, double *texels, uint64_t num_texels,
+                          lj_shape *shapes, uint64_t num_shapes, lj_light *lights, uint64_t num_lights);
 void lj_scene_destroy(lj_scene *scene);                        /* scene.cpp:67-71 */
 /* render(): rgb_out is w*h*3 f32, row-major, y=0 top (what imwrite keeps, image.cpp:146-149) */
 int lj_render(lj_scene *scene, const lj_render_params *params, float *rgb_out, lj_stats *stats);

@@ -42,7 +42,7 @@ class Stats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("extend_ms", C.c_double), ("shadow_ms", C.c_double),
                 ("shade_ms", C.c_double), ("generate_ms", C.c_double), ("bvh_nodes", C.c_uint64),
                 ("bvh_prims", C.c_uint64), ("shadow_nodes_visited", C.c_uint64), ("shadow_prims_tested", C.c_uint64),
-                ("iterations", C.c_uint64)]
+                ("iterations", C.c_uint64), ("tables_build_ms", C.c_double)]
 
     @property
     def rays(self):
@@ -68,7 +68,23 @@ HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("geom_id", "<i4
 ABI_SYMBOLS = ["lj_init", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", "lj_render", "lj_render_device",
                "lj_intersect_batch", "lj_scene_info", "lj_last_error", "lj_scene_desc_save", "lj_scene_desc_load",
                "lj_scene_desc_free", "lj_scene_desc_pin", "lj_image_encoded_size", "lj_image_encode", "lj_image_write",
-               "lj_accum_finalize", "lj_accum_encode", "lj_accum_write", "lj_accum_save", "lj_accum_load"]
+               "lj_accum_finalize", "lj_accum_encode", "lj_accum_write", "lj_accum_save", "lj_accum_load",
+               "lj_scene_create_ex", "lj_scene_read_derived"]
+
+SCENE_BUILD_TABLES = 1      # lj_scene_create_ex flags
+SCENE_POISON_DERIVED = 2
+
+# numpy mirrors of lj_shape / lj_light (include/lajolla_gpu.h) for reading record arrays
+SHAPE_DTYPE = np.dtype([("kind", "<i4"), ("material_id", "<i4"), ("area_light_id", "<i4"), ("interior_medium_id", "<i4"),
+                        ("exterior_medium_id", "<i4"), ("has_normals", "<i4"), ("has_uvs", "<i4"), ("_pad", "<i4"),
+                        ("center", "<f8", 3), ("radius", "<f8"), ("vertex_offset", "<u4"), ("num_vertices", "<u4"),
+                        ("triangle_offset", "<u4"), ("num_triangles", "<u4"), ("total_area", "<f8"),
+                        ("tri_cdf_offset", "<u8"), ("tri_pmf_offset", "<u8")])
+LIGHT_DTYPE = np.dtype([("kind", "<i4"), ("shape_id", "<i4"), ("intensity", "<f8", 3), ("values_texture", "<i4"), ("_pad", "<i4"),
+                        ("to_world", "<f8", 16), ("to_local", "<f8", 16), ("scale", "<f8"), ("dist_width", "<i4"),
+                        ("dist_height", "<i4"), ("cdf_rows_offset", "<u8"), ("pdf_rows_offset", "<u8"),
+                        ("cdf_marginals_offset", "<u8"), ("pdf_marginals_offset", "<u8"), ("total_values", "<f8")])
+IMAGE_DTYPE = np.dtype([("channels", "<i4"), ("num_levels", "<i4"), ("width", "<i4", 8), ("height", "<i4", 8), ("offset", "<u8", 8)])
 
 _lib = None
 
@@ -99,6 +115,8 @@ def load_library():
     lib.lj_scene_desc_free.argtypes = [C.c_void_p]
     lib.lj_scene_desc_free.restype = None
     lib.lj_scene_desc_pin.argtypes = [C.c_void_p, C.c_int]
+    lib.lj_scene_create_ex.argtypes = [C.c_void_p, C.c_void_p, C.c_uint32, C.POINTER(C.c_void_p)]
+    lib.lj_scene_read_derived.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64]
     lib.lj_image_encoded_size.argtypes = [C.c_int32, C.c_int32, C.c_int32]
     lib.lj_image_encoded_size.restype = C.c_uint64
     lib.lj_image_encode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
@@ -129,8 +147,8 @@ class LajollaGPU:
     def load_scene(self, blob_path, res=None, spp=None):
         return Scene(self, blob_path, res=res, spp=spp)
 
-    def scene_from_desc(self, desc):
-        return Scene(self, desc=desc)
+    def scene_from_desc(self, desc, flags=0):
+        return Scene(self, desc=desc, flags=flags)
 
     # ---- output step (imwrite, image.cpp:135-173) ----
     def encode_image(self, img, fmt):
@@ -195,6 +213,23 @@ class HostSceneDesc:
             opt[1] = int(spp)
         self.pinned = bool(pin) and self.lib.lj_scene_desc_pin(self.handle, 1) == 0
 
+    def _u64(self, off):
+        return C.c_uint64.from_address(self.handle.value + off).value
+
+    def _array(self, ptr_off, count, dtype):
+        ptr = C.c_void_p.from_address(self.handle.value + ptr_off).value
+        if not ptr or count == 0:
+            return np.zeros(0, dtype=dtype)
+        buf = (C.c_char * (count * np.dtype(dtype).itemsize)).from_address(ptr)
+        return np.frombuffer(buf, dtype=dtype)
+
+    def arrays(self):
+        """numpy views of the host arrays the scene-build step derives (offsets: see lj_scene_desc)."""
+        return {"shapes": self._array(400, self._u64(344), SHAPE_DTYPE), "lights": self._array(408, self._u64(352), LIGHT_DTYPE),
+                "images1": self._array(440, self._u64(384), IMAGE_DTYPE), "images3": self._array(448, self._u64(392), IMAGE_DTYPE),
+                "texels": self._array(528, self._u64(472), np.float64), "tables": self._array(536, self._u64(480), np.float64),
+                "light_pmf_offset": self._u64(552), "light_cdf_offset": self._u64(560)}
+
     def close(self):
         if self.handle:
             if self.pinned:
@@ -206,7 +241,7 @@ class HostSceneDesc:
 class Scene:
     """A flattened scene blob (.ljs, written by bin/lj_flatten or LJ_SAVE_SCENE) resident on the GPU."""
 
-    def __init__(self, gpu, blob_path=None, res=None, spp=None, desc=None):
+    def __init__(self, gpu, blob_path=None, res=None, spp=None, desc=None, flags=0):
         self.gpu = gpu
         lib = gpu.lib
         own = desc is None
@@ -214,7 +249,10 @@ class Scene:
             desc = HostSceneDesc(blob_path, res=res, spp=spp)
         self.handle = C.c_void_p()
         try:
-            _check(lib, lib.lj_scene_create(gpu.handle, desc.handle, C.byref(self.handle)), "lj_scene_create")
+            if flags:
+                _check(lib, lib.lj_scene_create_ex(gpu.handle, desc.handle, int(flags), C.byref(self.handle)), "lj_scene_create_ex")
+            else:
+                _check(lib, lib.lj_scene_create(gpu.handle, desc.handle, C.byref(self.handle)), "lj_scene_create")
         finally:
             if own:
                 desc.close()
@@ -222,6 +260,15 @@ class Scene:
         self.build_stats = Stats()
         _check(lib, lib.lj_scene_info(self.handle, C.byref(w), C.byref(h), C.byref(spp), C.byref(self.build_stats)), "lj_scene_info")
         self.width, self.height, self.spp = w.value, h.value, spp.value
+
+    def read_derived(self, num_tables, num_texels, num_shapes, num_lights):
+        """device copies of tables / texels / shape and light records (lj_scene_read_derived)"""
+        tables = np.empty(num_tables, dtype=np.float64); texels = np.empty(num_texels, dtype=np.float64)
+        shapes = np.empty(num_shapes, dtype=SHAPE_DTYPE); lights = np.empty(num_lights, dtype=LIGHT_DTYPE)
+        _check(self.gpu.lib, self.gpu.lib.lj_scene_read_derived(self.handle, tables.ctypes.data, num_tables, texels.ctypes.data, num_texels,
+                                                               shapes.ctypes.data, num_shapes, lights.ctypes.data, num_lights),
+               "lj_scene_read_derived")
+        return tables, texels, shapes, lights
 
     def render(self, params=None, out=None):
         """render(): host f32 image (h, w, 3), y=0 top.  `out` may be a pinned/host f32 array to fill."""

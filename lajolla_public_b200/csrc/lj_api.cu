@@ -108,6 +108,12 @@ static int validate_desc(const lj_scene_desc *d) {
 }
 
 extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene **out) {
+    uint32_t flags = 0;
+    if (const char *e = getenv("LJ_BUILD_TABLES")) if (atoi(e) != 0) flags |= LJ_SCENE_BUILD_TABLES;
+    return lj_scene_create_ex(ctx, desc, flags, out);
+}
+
+extern "C" int lj_scene_create_ex(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flags, lj_scene **out) {
     if (!ctx || !desc || !out) { lj_set_error("lj_scene_create: null argument"); return LJ_EINVAL; }
     int rc = validate_desc(desc);
     if (rc) return rc;
@@ -154,6 +160,12 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
     d.light_pmf = d.tables + desc->light_pmf_offset;
     d.light_cdf = d.tables + desc->light_cdf_offset;
     cudaEventRecord(e1);
+    if (flags & LJ_SCENE_BUILD_TABLES) {
+        float tms = 0;
+        if ((rc = lj_scene_build_tables(s, desc, (flags & LJ_SCENE_POISON_DERIVED) != 0, &tms)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+        s->build_stats.tables_build_ms = tms;
+        cudaEventRecord(e1);
+    }
 
     BvhBuildInput bi;
     bi.num_tris = (int)desc->num_indices; bi.num_spheres = (int)spheres.size();
@@ -170,7 +182,7 @@ extern "C" int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene 
     if (const char *bv = getenv("LJ_BVH")) if (atoi(bv) == 2) d.bvh8 = nullptr;
     if (d.bvh8) d.tri_verts = s->bvh.tri_verts8;
     float ms = 0;
-    cudaEventElapsedTime(&ms, e0, e1); s->build_stats.upload_ms = ms;
+    cudaEventElapsedTime(&ms, e0, e1); s->build_stats.upload_ms = ms - s->build_stats.tables_build_ms;
     cudaEventElapsedTime(&ms, e1, e2); s->build_stats.bvh_build_ms = ms;
     s->build_stats.bvh_nodes = s->bvh.bvh8 ? s->bvh.num_bvh8 : s->bvh.num_bvh2;
     s->build_stats.bvh_prims = s->bvh.num_prims;
@@ -184,6 +196,17 @@ extern "C" void lj_scene_destroy(lj_scene *s) {
     for (void *p : s->allocs) lj_free(p);
     lj_bvh_free(s->bvh);
     delete s;
+}
+
+extern "C" int lj_scene_read_derived(lj_scene *s, double *tables, uint64_t num_tables, double *texels, uint64_t num_texels,
+                                     lj_shape *shapes, uint64_t num_shapes, lj_light *lights, uint64_t num_lights) {
+    if (!s) { lj_set_error("lj_scene_read_derived: null scene"); return LJ_EINVAL; }
+    LJ_CUDA(cudaSetDevice(s->ctx->device));
+    if (tables && num_tables) LJ_CUDA(cudaMemcpy(tables, s->d.tables, sizeof(double) * num_tables, cudaMemcpyDeviceToHost));
+    if (texels && num_texels) LJ_CUDA(cudaMemcpy(texels, s->d.texels, sizeof(double) * num_texels, cudaMemcpyDeviceToHost));
+    if (shapes && num_shapes) LJ_CUDA(cudaMemcpy(shapes, s->d.shapes, sizeof(lj_shape) * num_shapes, cudaMemcpyDeviceToHost));
+    if (lights && num_lights) LJ_CUDA(cudaMemcpy(lights, s->d.lights, sizeof(lj_light) * num_lights, cudaMemcpyDeviceToHost));
+    return LJ_OK;
 }
 
 extern "C" int lj_scene_info(lj_scene *s, int32_t *width, int32_t *height, int32_t *spp, lj_stats *build_stats) {

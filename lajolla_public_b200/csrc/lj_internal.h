@@ -37,5 +37,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
 int lj_render_aux(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st);
 int lj_render_volpath(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st);
 int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st);
+// scene.cpp:36-52 on the device (lj_scene_build.cu)
+int lj_scene_build_tables(lj_scene *s, const lj_scene_desc *desc, bool poison, float *elapsed_ms);
 
 #define LJ_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { lj_set_error("%s failed: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); return LJ_ECUDA; } } while (0)
