@@ -114,15 +114,14 @@ struct Trav8 {
         // Child plane along one axis: t = q * A + B with A = 2^e / d, B = (p - o) / d, q the quantised
         // byte.  The byte is spliced into the mantissa of 2^15 with one PRMT (M = 32768 + q, exact), so
         // t = fma(M, A, C) with C = B - 32768 A: one PRMT + one FFMA per plane, no int->float conversion.
-        // C carries up to |A|/512 of rounding error per rounding; the near (far) planes are moved out by
-        // |A|/128, i.e. boxes grow by < 1 % of a quantisation step, and stay conservative.
-        const float ax = __uint_as_float(byte_of(ew, 0) << 23) * idx;
-        const float ay = __uint_as_float(byte_of(ew, 1) << 23) * idy;
-        const float az = __uint_as_float(byte_of(ew, 2) << 23) * idz;
-        const float cx = fmaf(-32768.0f, ax, (n0.x - r.ox) * idx);
-        const float cy = fmaf(-32768.0f, ay, (n0.y - r.oy) * idy);
-        const float cz = fmaf(-32768.0f, az, (n0.z - r.oz) * idz);
-        const float px = fabsf(ax) * 0.0078125f, py = fabsf(ay) * 0.0078125f, pz = fabsf(az) * 0.0078125f;
+        // Rounding: A is off by 2^-24 relative (the reciprocal), B by 3 roundings, C by one more and by the
+        // cancellation against 32768 A, t by its own rounding: |t~ - t| <= 2^-24 (|t| + 4 |C| + 5 * 32768 |A|)
+        // <= 2^-24 * 5 |C| + 0.012 |A|.  The near (far) planes are therefore moved out by |A|/64 + |C| * 2^-21 once
+        // per node and axis; boxes grow by < 2 % of a quantisation step and the test stays conservative without
+        // any per-child padding.
+        const float px = fmaf(fabsf(cx), 4.76837158e-7f, fabsf(ax) * 0.015625f);
+        const float py = fmaf(fabsf(cy), 4.76837158e-7f, fabsf(ay) * 0.015625f);
+        const float pz = fmaf(fabsf(cz), 4.76837158e-7f, fabsf(az) * 0.015625f);
         const float c0x = cx - px, c1x = cx + px, c0y = cy - py, c1y = cy + py, c0z = cz - pz, c1z = cz + pz;
         const unsigned oct4 = oct_inv * 0x01010101u;
         unsigned hitmask = 0;
@@ -148,8 +147,7 @@ struct Trav8 {
                 const float t0z = fmaf(byte_to_m15(nz, j), az, c0z), t1z = fmaf(byte_to_m15(fz, j), az, c1z);
                 const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
                 const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, best_t));
-                // relative padding on top (B is computed with a few roundings)
-                if (fmaf(fabsf(t0), -2e-6f, t0) <= fmaf(fabsf(t1), 2e-6f, t1))
+                if (t0 <= t1)
                     hitmask |= byte_of(bits4, j) << byte_of(index4, j);
             }
         }
