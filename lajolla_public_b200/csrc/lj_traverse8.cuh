@@ -119,7 +119,13 @@ struct Trav8 {
         // <= 2^-24 * 5 |C| + 0.012 |A|.  The near (far) planes are therefore moved out by |A|/64 + |C| * 2^-21 once
         // per node and axis; boxes grow by < 2 % of a quantisation step and the test stays conservative without
         // any per-child padding.
-        const float px = fmaf(fabsf(cx), 4.76837158e-7f, fabsf(ax) * 0.015625f);
+        const float ax = __uint_as_float(byte_of(ew, 0) << 23) * idx;
+        const float ay = __uint_as_float(byte_of(ew, 1) << 23) * idy;
+        const float az = __uint_as_float(byte_of(ew, 2) << 23) * idz;
+        const float cx = fmaf(-32768.0f, ax, (n0.x - r.ox) * idx);
+        const float cy = fmaf(-32768.0f, ay, (n0.y - r.oy) * idy);
+        const float cz = fmaf(-32768.0f, az, (n0.z - r.oz) * idz);
+        const float px =fmaf(fabsf(cx), 4.76837158e-7f, fabsf(ax) * 0.015625f);
         const float py = fmaf(fabsf(cy), 4.76837158e-7f, fabsf(ay) * 0.015625f);
         const float pz = fmaf(fabsf(cz), 4.76837158e-7f, fabsf(az) * 0.015625f);
         const float c0x = cx - px, c1x = cx + px, c0y = cy - py, c1y = cy + py, c0z = cz - pz, c1z = cz + pz;
