@@ -85,16 +85,27 @@ def test_many_spp_same_streams(gpu, manifest, name, engine):
     assert abs(float(img.mean()) - float(ref.mean())) <= 0.01 * float(ref.mean())
 
 
-def test_cbox_1024spp_rmse_vs_reference_render(gpu, manifest):
-    """BASELINE.json north star, threshold (ii): at 1024 spp the image RMSE against the reference's
-    own CPU render (mode A = the reference's render(), per-tile streams) is below a stated bound.
-    Bound: 2 x the noise floor RMSE(ref_A1024, ref_B1024) of two independent oracle renders
-    (0.0178 for cbox at 128x128 => bound 0.0356); secondary: relMSE with 0.1 % trimming <= 2 x floor.
-    The GPU renders on per-sample streams with the wavefront engine, i.e. independent of render A."""
+RMSE_SCENES = ["cbox", "veach_mi", "sponza", "matpreview", "disney_bsdf", "volpath_test3", "vol_cbox", "hetvol"]
+
+
+@pytest.mark.parametrize("name", RMSE_SCENES)
+def test_1024spp_rmse_vs_reference_render(gpu, manifest, name):
+    """BASELINE.json north star, threshold (ii), one case per config: at 1024 spp the image RMSE against the
+    reference's own CPU render (mode A = the reference's render(), per-tile streams) is below a stated bound.
+    Bound: 2 x the noise floor RMSE(ref_A1024, ref_B1024) of two independent oracle renders of that scene
+    (cbox at 128x128: floor 0.0178 => bound 0.0356; the others are printed and recorded in BASELINE.md);
+    secondary: relMSE with 0.1 % trimming <= 2 x its floor.  The GPU renders on per-sample streams with the
+    wavefront engine, i.e. independent of render A; against render B (identical streams) it must be ~0."""
     from lajolla_public_b200 import RenderParams, RNG_SAMPLE_STREAMS, ENGINE_WAVEFRONT
-    d, entry, scene = load_case(gpu, manifest, "cbox")
-    ref_a = np.load(os.path.join(d, "cbox_A1024.npy"))
-    ref_b = np.load(os.path.join(d, "cbox_B1024.npy"))
+    d = fixture_dir(name)
+    if d is None:
+        pytest.skip(f"fixture {name}.ljs not present (big fixtures live in git-ignored scenes_flat/)")
+    entry = manifest[name]
+    res = entry["res"] if "A1024" in entry["images"] else entry["rmse1024"]["res"]
+    scene = gpu.load_scene(os.path.join(d, name + ".ljs"), res=res)
+    gold = os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden")
+    ref_a = np.load(os.path.join(gold, f"{name}_A1024.npy"))
+    ref_b = np.load(os.path.join(gold, f"{name}_B1024.npy"))
     img, st = scene.render(RenderParams(spp=1024, rng_mode=RNG_SAMPLE_STREAMS, engine=ENGINE_WAVEFRONT))
     scene.close()
 
@@ -108,8 +119,10 @@ def test_cbox_1024spp_rmse_vs_reference_render(gpu, manifest):
     floor, floor_rel = rmse(ref_a, ref_b), relmse(ref_a, ref_b)
     got, got_rel = rmse(img, ref_a), relmse(img, ref_a)
     same = rmse(img, ref_b)
-    print(f"cbox 1024 spp: RMSE vs reference render {got:.5f} (floor {floor:.5f}, bound {2 * floor:.5f}); relMSE {got_rel:.3e} "
-          f"(floor {floor_rel:.3e}); RMSE vs oracle on identical streams {same:.3e}; {st.rays / st.render_ms * 1e-3:.0f} Mrays/s")
+    print(f"{name} {res[0]}x{res[1]} 1024 spp: RMSE vs reference render {got:.5f} (floor {floor:.5f}, bound {2 * floor:.5f}); "
+          f"relMSE {got_rel:.3e} (floor {floor_rel:.3e}); RMSE vs oracle on identical streams {same:.3e}; "
+          f"{st.rays / st.render_ms * 1e-3:.0f} Mrays/s, {res[0] * res[1] * 1024 / st.render_ms * 1e-3:.1f} Msamples/s")
     assert got <= 2 * floor
     assert got_rel <= 2 * floor_rel
-    assert same <= 1e-3 * float(ref_b.mean())       # identical streams: only rare flipped decisions may differ
+    # identical streams: only rare flipped decisions (last-ulp differences of libm functions) may differ
+    assert same <= max(1e-3 * float(ref_b.mean()), 0.05 * floor)

@@ -52,6 +52,19 @@ CASES = [
 ]
 
 
+# north-star threshold (ii): 1024-spp oracle renders (mode A = the reference's render(), mode B = per-sample
+# streams) at a reduced film size; images only (a few hundred KB each), always committed to tests/golden/.
+RMSE_CASES = [
+    ("veach_mi", "veach_mi/mi.xml", (96, 64)),
+    ("sponza", "sponza/sponza.xml", (128, 96)),
+    ("matpreview", "matpreview/matpreview.xml", (114, 85)),
+    ("disney_bsdf", "disney_bsdf_test/disney_bsdf.xml", (114, 85)),
+    ("volpath_test3", "volpath_test/volpath_test3.xml", (64, 64)),
+    ("vol_cbox", "volpath_test/vol_cbox.xml", (64, 64)),
+    ("hetvol", "volpath_test/hetvol.xml", (64, 48)),
+]
+
+
 def run(cmd):
     r = subprocess.run(cmd, stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True)
     if r.returncode != 0:
@@ -80,7 +93,32 @@ def imwrite_kat():
     print(f"  imwrite_kat: {w}x{h} -> .exr {os.path.getsize(os.path.join(gold, 'imwrite_kat.exr'))} B, .pfm {os.path.getsize(os.path.join(gold, 'imwrite_kat.pfm'))} B")
 
 
+def rmse_goldens(only):
+    """python tools/make_goldens.py --rmse [names]: mint <name>_{A,B}1024.npy + manifest[name]["rmse1024"]."""
+    manifest_path = os.path.join(ROOT, "tests/golden/manifest.json")
+    manifest = json.load(open(manifest_path))
+    for name, xml, res in RMSE_CASES:
+        if only and name not in only:
+            continue
+        xml_path = os.path.join(REF, "scenes", xml)
+        entry = {"res": list(res), "images": {}}
+        for mode in ("A", "B"):
+            pfm = f"/tmp/lj_golden_{name}_{mode}1024.pfm"
+            out = run([DRIVER, "render", xml_path, "-o", pfm, "--mode", mode, "--spp", "1024", "--res", str(res[0]), str(res[1])])
+            stats = json.loads([l for l in out.splitlines() if l.startswith("{")][-1])
+            img = read_pfm(pfm)
+            np.save(os.path.join(ROOT, "tests/golden", f"{name}_{mode}1024.npy"), img)
+            entry["images"][f"{mode}1024"] = {"intersect_rays": stats["intersect_rays"], "occluded_rays": stats["occluded_rays"],
+                                              "mean": float(img.mean()), "render_s": stats["render_s"], "threads": stats["threads"]}
+            os.remove(pfm)
+            print(f"  {name} {mode}1024 {res}: mean {img.mean():.6f}, {stats['render_s']:.1f} s on {stats['threads']} threads", flush=True)
+        manifest[name]["rmse1024"] = entry
+        json.dump(manifest, open(manifest_path, "w"), indent=1, sort_keys=True)
+
+
 def main():
+    if len(sys.argv) > 1 and sys.argv[1] == "--rmse":
+        return rmse_goldens(set(sys.argv[2:]))
     only = set(sys.argv[1:])
     if not only or "imwrite_kat" in only:
         imwrite_kat()
@@ -107,6 +145,8 @@ def main():
                                     "mean": float(img.mean())}
             os.remove(pfm)
             print(f"  {name} {key}: mean {img.mean():.6f}, rays {stats['intersect_rays']}+{stats['occluded_rays']}")
+        if name in manifest and "rmse1024" in manifest[name]:
+            entry["rmse1024"] = manifest[name]["rmse1024"]
         manifest[name] = entry
     json.dump(manifest, open(manifest_path, "w"), indent=1, sort_keys=True)
 
