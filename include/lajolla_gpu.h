@@ -254,6 +254,44 @@ int lj_accum_save(lj_ctx *ctx, const char *filename, const double *dev_sum, int3
 int lj_accum_load(lj_ctx *ctx, const char *filename, double *dev_sum, int32_t width, int32_t height,
                   int32_t *sample_begin, int32_t *sample_end);
 
+/* ---- on-disk asset formats decoded on the device ----
+ * The loaders the reference's parser calls for every <shape type="obj|serialized"> and <volume type="gridvolume">
+ * (parse_scene.cpp), taking the file's bytes and returning what the reference's TriangleMesh / GridVolume hold:
+ *   lj_mesh_load_obj         parse_obj(filename, to_world)                    parse_obj.cpp:137-234
+ *   lj_mesh_load_serialized  load_serialized(filename, shape_index, to_world) load_serialized.cpp:174-256
+ *   lj_mesh_compute_normals  compute_normal(vertices, indices)                parse_obj.cpp:57-92
+ *   lj_volume_load           load_volume_from_file<Real|Spectrum>(filename)   volume.cpp:6-115
+ * `to_world` / `to_local` are row-major 4x4 (to_local = the reference's inverse(to_world), matrix.h:80).
+ * Output arrays are host memory owned by the library until lj_mesh_free / lj_volume_free.  Results are bit-identical
+ * to the reference's loaders, except normals produced by compute_normal (the device's asin(), last ulp).  OBJ numbers
+ * outside the exactly convertible range (see csrc/lj_assets.cu) are refused with LJ_EUNSUPPORTED, n-gons with
+ * LJ_EINVAL (the reference's Error()). */
+typedef struct lj_mesh_data {      /* TriangleMesh, shape.h:39-49 */
+    uint64_t num_vertices, num_triangles;
+    int32_t has_normals, has_uvs;
+    double *positions;             /* 3 per vertex */
+    double *normals;               /* 3 per vertex, NULL without normals */
+    double *uvs;                   /* 2 per vertex, NULL without uvs */
+    int32_t *indices;              /* 3 per triangle */
+    double decode_ms;              /* device time of the decode kernels */
+} lj_mesh_data;
+typedef struct lj_volume_data {    /* GridVolume<Real|Spectrum>, volume.h:19-26 (scale = 1) */
+    int32_t resolution[3], channels;
+    double p_min[3], p_max[3], max_data[3];
+    double *data;                  /* channels doubles per voxel, x fastest */
+    uint64_t num_values;
+    double decode_ms;
+} lj_volume_data;
+int lj_mesh_load_obj(lj_ctx *ctx, const void *text, uint64_t text_bytes, const double *to_world, const double *to_local,
+                     lj_mesh_data *out);
+int lj_mesh_load_serialized(lj_ctx *ctx, const void *file, uint64_t file_bytes, int32_t shape_index,
+                            const double *to_world, const double *to_local, lj_mesh_data *out);
+int lj_mesh_compute_normals(lj_ctx *ctx, const double *positions, uint64_t num_vertices, const int32_t *indices,
+                            uint64_t num_triangles, double *normals_out);
+void lj_mesh_free(lj_mesh_data *mesh);
+int lj_volume_load(lj_ctx *ctx, const void *file, uint64_t file_bytes, int32_t target_channels, lj_volume_data *out);
+void lj_volume_free(lj_volume_data *vol);
+
 #ifdef __cplusplus
 }
 #endif

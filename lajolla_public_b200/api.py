@@ -69,7 +69,8 @@ ABI_SYMBOLS = ["lj_init", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", 
                "lj_intersect_batch", "lj_scene_info", "lj_last_error", "lj_scene_desc_save", "lj_scene_desc_load",
                "lj_scene_desc_free", "lj_scene_desc_pin", "lj_image_encoded_size", "lj_image_encode", "lj_image_write",
                "lj_accum_finalize", "lj_accum_encode", "lj_accum_write", "lj_accum_save", "lj_accum_load",
-               "lj_scene_create_ex", "lj_scene_read_derived"]
+               "lj_scene_create_ex", "lj_scene_read_derived", "lj_mesh_load_obj", "lj_mesh_load_serialized",
+               "lj_mesh_compute_normals", "lj_mesh_free", "lj_volume_load", "lj_volume_free"]
 
 SCENE_BUILD_TABLES = 1      # lj_scene_create_ex flags
 SCENE_POISON_DERIVED = 2
@@ -86,6 +87,20 @@ LIGHT_DTYPE = np.dtype([("kind", "<i4"), ("shape_id", "<i4"), ("intensity", "<f8
                         ("cdf_marginals_offset", "<u8"), ("pdf_marginals_offset", "<u8"), ("total_values", "<f8")])
 IMAGE_DTYPE = np.dtype([("channels", "<i4"), ("num_levels", "<i4"), ("width", "<i4", 8), ("height", "<i4", 8), ("offset", "<u8", 8)])
 
+
+
+class MeshData(C.Structure):       # lj_mesh_data
+    _fields_ = [("num_vertices", C.c_uint64), ("num_triangles", C.c_uint64), ("has_normals", C.c_int32), ("has_uvs", C.c_int32),
+                ("positions", C.POINTER(C.c_double)), ("normals", C.POINTER(C.c_double)), ("uvs", C.POINTER(C.c_double)),
+                ("indices", C.POINTER(C.c_int32)), ("decode_ms", C.c_double)]
+
+
+class VolumeData(C.Structure):     # lj_volume_data
+    _fields_ = [("resolution", C.c_int32 * 3), ("channels", C.c_int32), ("p_min", C.c_double * 3), ("p_max", C.c_double * 3),
+                ("max_data", C.c_double * 3), ("data", C.POINTER(C.c_double)), ("num_values", C.c_uint64), ("decode_ms", C.c_double)]
+
+
+_IDENTITY = np.eye(4, dtype=np.float64)
 _lib = None
 
 
@@ -126,6 +141,14 @@ def load_library():
     lib.lj_accum_write.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
     lib.lj_accum_save.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
     lib.lj_accum_load.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.POINTER(C.c_int32), C.POINTER(C.c_int32)]
+    lib.lj_mesh_load_obj.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.c_void_p, C.c_void_p, C.POINTER(MeshData)]
+    lib.lj_mesh_load_serialized.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.c_int32, C.c_void_p, C.c_void_p, C.POINTER(MeshData)]
+    lib.lj_mesh_compute_normals.argtypes = [C.c_void_p, C.c_void_p, C.c_uint64, C.c_void_p, C.c_uint64, C.c_void_p]
+    lib.lj_mesh_free.argtypes = [C.POINTER(MeshData)]
+    lib.lj_mesh_free.restype = None
+    lib.lj_volume_load.argtypes = [C.c_void_p, C.c_char_p, C.c_uint64, C.c_int32, C.POINTER(VolumeData)]
+    lib.lj_volume_free.argtypes = [C.POINTER(VolumeData)]
+    lib.lj_volume_free.restype = None
     _lib = lib
     return lib
 
@@ -187,6 +210,60 @@ class LajollaGPU:
         b, e = C.c_int32(), C.c_int32()
         _check(self.lib, self.lib.lj_accum_load(self.handle, os.fsencode(path), C.c_void_p(dev_ptr), w, h, C.byref(b), C.byref(e)), "lj_accum_load")
         return b.value, e.value
+
+    # ---- on-disk asset formats decoded on the device (parse_obj / load_serialized / load_volume_from_file) ----
+    def _mesh_out(self, m):
+        nv, nt = int(m.num_vertices), int(m.num_triangles)
+
+        def arr(ptr, count, dtype, shape):
+            if not ptr or count == 0:
+                return np.zeros(shape, dtype=dtype)
+            return np.ctypeslib.as_array(ptr, shape=(count,)).astype(dtype, copy=True).reshape(shape)
+        out = {"positions": arr(m.positions, nv * 3, np.float64, (nv, 3)),
+               "normals": arr(m.normals, nv * 3, np.float64, (nv, 3)) if m.has_normals else np.zeros((0, 3)),
+               "uvs": arr(m.uvs, nv * 2, np.float64, (nv, 2)) if m.has_uvs else np.zeros((0, 2)),
+               "indices": arr(m.indices, nt * 3, np.int32, (nt, 3)), "decode_ms": m.decode_ms}
+        self.lib.lj_mesh_free(C.byref(m))
+        return out
+
+    @staticmethod
+    def _xforms(to_world, to_local):
+        tw = np.ascontiguousarray(_IDENTITY if to_world is None else to_world, dtype=np.float64).reshape(4, 4)
+        tl = np.ascontiguousarray(np.linalg.inv(tw) if to_local is None else to_local, dtype=np.float64).reshape(4, 4)
+        return tw, tl
+
+    def load_obj(self, data, to_world=None, to_local=None):
+        """parse_obj(file, to_world) on the device; `data` = the file's bytes.  Pass the reference's inverse(to_world)
+        as `to_local` for bit-identical normals (numpy's inverse is used otherwise)."""
+        tw, tl = self._xforms(to_world, to_local)
+        m = MeshData()
+        _check(self.lib, self.lib.lj_mesh_load_obj(self.handle, data, len(data), tw.ctypes.data, tl.ctypes.data, C.byref(m)), "lj_mesh_load_obj")
+        return self._mesh_out(m)
+
+    def load_serialized(self, data, shape_index=0, to_world=None, to_local=None):
+        tw, tl = self._xforms(to_world, to_local)
+        m = MeshData()
+        _check(self.lib, self.lib.lj_mesh_load_serialized(self.handle, data, len(data), int(shape_index), tw.ctypes.data, tl.ctypes.data, C.byref(m)),
+               "lj_mesh_load_serialized")
+        return self._mesh_out(m)
+
+    def compute_normals(self, positions, indices):
+        pos = np.ascontiguousarray(positions, dtype=np.float64).reshape(-1, 3)
+        idx = np.ascontiguousarray(indices, dtype=np.int32).reshape(-1, 3)
+        out = np.empty_like(pos)
+        _check(self.lib, self.lib.lj_mesh_compute_normals(self.handle, pos.ctypes.data, pos.shape[0], idx.ctypes.data, idx.shape[0], out.ctypes.data),
+               "lj_mesh_compute_normals")
+        return out
+
+    def load_volume(self, data, channels=3):
+        v = VolumeData()
+        _check(self.lib, self.lib.lj_volume_load(self.handle, data, len(data), int(channels), C.byref(v)), "lj_volume_load")
+        res = tuple(v.resolution)
+        grid = np.ctypeslib.as_array(v.data, shape=(int(v.num_values),)).copy().reshape(res[2], res[1], res[0], channels)
+        out = {"resolution": res, "p_min": np.array(v.p_min), "p_max": np.array(v.p_max), "max_data": np.array(v.max_data)[:channels],
+               "data": grid, "decode_ms": v.decode_ms}
+        self.lib.lj_volume_free(C.byref(v))
+        return out
 
     def close(self):
         if self.handle:

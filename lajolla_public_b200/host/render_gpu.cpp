@@ -20,6 +20,7 @@
 #include "flexception.h"
 #include "scene_flatten.h"
 #include "lajolla_gpu.h"
+#include "host_ctx.h"
 
 #include <cstdio>
 #include <cstdlib>
@@ -32,15 +33,20 @@ static void check(int rc, const char *what) {
     if (rc != LJ_OK) Error(std::string(what) + " failed: " + lj_last_error());
 }
 
+lj_ctx *lj_host_ctx() {
+    if (!g_ctx) {
+        int dev = getenv("LJ_DEVICE") ? atoi(getenv("LJ_DEVICE")) : 0;
+        check(lj_init(dev, &g_ctx), "lj_init");
+    }
+    return g_ctx;
+}
+
 Image3 render(const Scene &scene) {
     FlatScene fs;
     flatten_scene(scene, fs);
     if (const char *p = getenv("LJ_SAVE_SCENE")) check(lj_scene_desc_save(&fs.desc, p), "lj_scene_desc_save");
 
-    if (!g_ctx) {
-        int dev = getenv("LJ_DEVICE") ? atoi(getenv("LJ_DEVICE")) : 0;
-        check(lj_init(dev, &g_ctx), "lj_init");
-    }
+    lj_host_ctx();
     lj_scene *gs = nullptr;
     check(lj_scene_create(g_ctx, &fs.desc, &gs), "lj_scene_create");
 

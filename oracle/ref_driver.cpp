@@ -24,12 +24,23 @@
 //       the reference's imwrite() (image.cpp:135-173) applied to a raw image
 //       {int32 w, h; float rgb[h][w][3]} (widened to the Image3 doubles imwrite takes):
 //       the golden generator for the output-encode step.
+//   ref_driver mesh <file.obj|file.serialized> <shape_index> <out.bin> [16 doubles: to_world, row major]
+//       the reference's parse_obj() (parse_obj.cpp:137-234) / load_serialized()
+//       (load_serialized.cpp:174-256) applied to an asset file; dumps
+//       {u64 nv, nt, n_normals, n_uvs; f64 to_world[16], inverse(to_world)[16];
+//        f64 positions[nv][3], normals[..][3], uvs[..][2]; i32 indices[nt][3]}.
+//   ref_driver vol <file.vol> <1|3> <out.bin>
+//       the reference's load_volume_from_file<Real|Spectrum>() (volume.cpp:6-115); dumps
+//       {i32 res[3], channels; f64 p_min[3], p_max[3], max_data[channels], data[nvox][channels]}.
 //   ref_driver rng <n>
 //       first n next_pcg32_real<double> draws of init_pcg32(7) (known-answer
 //       vector for pcg.h:32-67).
 #include "render.cpp"   // found via -I$(REF)/src : /root/reference/src/render.cpp
 
 #include "parse_scene.h"
+#include "parse_obj.h"
+#include "load_serialized.h"
+#include "volume.h"
 #include "timer.h"
 #include <chrono>
 #include <unistd.h>
@@ -184,6 +195,53 @@ static int cmd_imwrite(int argc, char **argv) {
     return 0;
 }
 
+static int cmd_mesh(int argc, char **argv) {
+    if (argc < 5) { fprintf(stderr, "usage: ref_driver mesh file shape_index out.bin [16 doubles]\n"); return 2; }
+    std::string file = argv[2];
+    int shape_index = atoi(argv[3]);
+    Matrix4x4 to_world = Matrix4x4::identity();
+    if (argc >= 5 + 16) for (int i = 0; i < 16; i++) to_world(i / 4, i % 4) = strtod(argv[5 + i], nullptr);
+    bool serialized = file.size() > 11 && file.substr(file.size() - 11) == ".serialized";
+    TriangleMesh mesh = serialized ? load_serialized(file, shape_index, to_world) : parse_obj(file, to_world);
+    Matrix4x4 inv = inverse(to_world);
+    std::ofstream f(argv[4], std::ios::binary);
+    uint64_t hdr[4] = {mesh.positions.size(), mesh.indices.size(), mesh.normals.size(), mesh.uvs.size()};
+    f.write((const char *)hdr, sizeof hdr);
+    for (int i = 0; i < 16; i++) { double v = to_world(i / 4, i % 4); f.write((const char *)&v, 8); }
+    for (int i = 0; i < 16; i++) { double v = inv(i / 4, i % 4); f.write((const char *)&v, 8); }
+    for (auto &p : mesh.positions) { double v[3] = {p[0], p[1], p[2]}; f.write((const char *)v, 24); }
+    for (auto &p : mesh.normals) { double v[3] = {p[0], p[1], p[2]}; f.write((const char *)v, 24); }
+    for (auto &p : mesh.uvs) { double v[2] = {p[0], p[1]}; f.write((const char *)v, 16); }
+    for (auto &t : mesh.indices) { int v[3] = {t[0], t[1], t[2]}; f.write((const char *)v, 12); }
+    printf("mesh %s: %zu vertices, %zu triangles, %zu normals, %zu uvs\n", file.c_str(), mesh.positions.size(),
+           mesh.indices.size(), mesh.normals.size(), mesh.uvs.size());
+    return 0;
+}
+
+static int cmd_vol(int argc, char **argv) {
+    if (argc < 5) { fprintf(stderr, "usage: ref_driver vol file.vol 1|3 out.bin\n"); return 2; }
+    int ch = atoi(argv[3]);
+    std::ofstream f(argv[4], std::ios::binary);
+    auto head = [&](const Vector3i &res, const Vector3 &a, const Vector3 &b) {
+        int r[4] = {res[0], res[1], res[2], ch}; f.write((const char *)r, 16);
+        double v[6] = {a[0], a[1], a[2], b[0], b[1], b[2]}; f.write((const char *)v, 48);
+    };
+    if (ch == 1) {
+        GridVolume<Real> g = load_volume_from_file<Real>(argv[2]);
+        head(g.resolution, g.p_min, g.p_max);
+        f.write((const char *)&g.max_data, 8);
+        f.write((const char *)g.data.data(), g.data.size() * 8);
+        printf("vol %s: %d x %d x %d, max %.17g\n", argv[2], g.resolution[0], g.resolution[1], g.resolution[2], g.max_data);
+    } else {
+        GridVolume<Spectrum> g = load_volume_from_file<Spectrum>(argv[2]);
+        head(g.resolution, g.p_min, g.p_max);
+        double m[3] = {g.max_data[0], g.max_data[1], g.max_data[2]}; f.write((const char *)m, 24);
+        for (auto &p : g.data) { double v[3] = {p[0], p[1], p[2]}; f.write((const char *)v, 24); }
+        printf("vol %s: %d x %d x %d x 3, max %.17g %.17g %.17g\n", argv[2], g.resolution[0], g.resolution[1], g.resolution[2], m[0], m[1], m[2]);
+    }
+    return 0;
+}
+
 static int cmd_rng(int argc, char **argv) {
     int n = argc > 2 ? atoi(argv[2]) : 8;
     pcg32_state rng = init_pcg32(7);
@@ -192,11 +250,13 @@ static int cmd_rng(int argc, char **argv) {
 }
 
 int main(int argc, char **argv) {
-    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|hits|imwrite|rng ...\n"); return 2; }
+    if (argc < 2) { fprintf(stderr, "usage: ref_driver render|hits|imwrite|mesh|vol|rng ...\n"); return 2; }
     std::string cmd = argv[1];
     if (cmd == "render") return cmd_render(argc, argv);
     if (cmd == "hits") return cmd_hits(argc, argv);
     if (cmd == "imwrite") return cmd_imwrite(argc, argv);
+    if (cmd == "mesh") return cmd_mesh(argc, argv);
+    if (cmd == "vol") return cmd_vol(argc, argv);
     if (cmd == "rng") return cmd_rng(argc, argv);
     fprintf(stderr, "unknown command %s\n", cmd.c_str());
     return 2;

@@ -52,10 +52,26 @@ def main():
         entry = {"width": sc.width, "height": sc.height, "spp": spp, "bvh_build_ms": sc.build_stats.bvh_build_ms}
         for ename, eng in (("wavefront", ENGINE_WAVEFRONT), ("megakernel", ENGINE_MEGAKERNEL)):
             rp = RenderParams(spp=spp, rng_mode=RNG_SAMPLE_STREAMS, engine=eng)
-            sc.render(RenderParams(spp=min(spp, 4), rng_mode=RNG_SAMPLE_STREAMS, engine=eng))   # warm-up
+            sc.render(RenderParams(spp=spp, rng_mode=RNG_SAMPLE_STREAMS, engine=eng))   # warm-up at the same spp (the slot arena is sized from it)
             _, st = sc.render(rp)
             entry[ename] = {"render_ms": st.render_ms, "msamples_per_s": st.samples / st.render_ms * 1e-3,
                             "mrays_per_s": st.rays / st.render_ms * 1e-3, "rays_per_sample": st.rays / max(st.samples, 1)}
+        # counting pass (flags bit0: nodes / primitives per ray; bit1: per-stage CUDA-event sums) of the wavefront engine:
+        # the per-scene N-bar figures and the algorithmic bytes per ray of SURVEY 8(d) / BASELINE.md section 4
+        _, st = sc.render(RenderParams(spp=spp, rng_mode=RNG_SAMPLE_STREAMS, engine=ENGINE_WAVEFRONT, flags=3))
+        closest = st.rays_primary + st.rays_extension
+        if closest:
+            nn, npr = st.nodes_visited / closest, st.prims_tested / closest
+            sn, sp = (st.shadow_nodes_visited / st.rays_shadow, st.shadow_prims_tested / st.rays_shadow) if st.rays_shadow else (0.0, 0.0)
+            bpr, sbpr = 32 + 20 + 80 * nn + 48 * npr, 32 + 4 + 80 * sn + 48 * sp
+            wf = entry["wavefront"]
+            entry["counting"] = {"rays_primary": st.rays_primary, "rays_extension": st.rays_extension, "rays_shadow": st.rays_shadow,
+                                 "nodes_per_ray": nn, "prims_per_ray": npr, "bytes_per_ray": bpr,
+                                 "shadow_nodes_per_ray": sn, "shadow_prims_per_ray": sp, "shadow_bytes_per_ray": sbpr,
+                                 "extend_ms": st.extend_ms, "shadow_ms": st.shadow_ms, "shade_ms": st.shade_ms, "generate_ms": st.generate_ms,
+                                 "iterations": st.iterations, "bvh_nodes": st.bvh_nodes, "bvh_prims": st.bvh_prims,
+                                 # whole-render algorithmic GB/s: (closest-hit rays x B/ray + shadow rays x B/ray) / timed render
+                                 "algorithmic_gbps_whole_render": (closest * bpr + st.rays_shadow * sbpr) / (wf["render_ms"] * 1e-3) * 1e-9}
         sc.close()
         if want_cpu:
             r = cpu(name, manifest, max(1, spp // 16))
