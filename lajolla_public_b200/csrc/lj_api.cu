@@ -178,6 +178,7 @@ extern "C" int lj_scene_create_ex(lj_ctx *ctx, const lj_scene_desc *desc, uint32
     d.tri_verts = s->bvh.tri_verts; d.spheres = d_spheres;
     d.bvh2 = s->bvh.bvh2; d.bvh2_root = s->bvh.bvh2_root;
     d.bvh8 = s->bvh.bvh8;
+    d.m15_bits = 0x47000000u;
     // LJ_BVH=2 keeps the binary tree for traversal (validation of the 8-wide path against it)
     if (const char *bv = getenv("LJ_BVH")) if (atoi(bv) == 2) d.bvh8 = nullptr;
     if (d.bvh8) d.tri_verts = s->bvh.tri_verts8;

@@ -51,6 +51,10 @@ struct DScene {
     const SpherePrim *spheres;
     const Bvh2Node *bvh2; int bvh2_root;
     const Bvh8Node *bvh8;
+    // 0x47000000 (the bits of 2^15) as a kernel-parameter value: the node test splices plane bytes into its mantissa with
+    // PRMT, and PRMT has one immediate operand -- with this one opaque to the compiler the per-child selector becomes the
+    // immediate and the constant comes from the constant bank, instead of four selector registers re-materialised per use
+    unsigned m15_bits;
 };
 
 // intersection.h:15-35

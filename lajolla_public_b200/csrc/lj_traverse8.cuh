@@ -23,8 +23,9 @@
 LJ_D unsigned byte_of(unsigned w, int i) { return (w >> (8 * i)) & 0xffu; }
 
 // byte j of w spliced into the mantissa of 2^15: returns the float 32768 + byte (exact)
-LJ_D float byte_to_m15(unsigned w, int j) {
-    return __uint_as_float(__byte_perm(w, 0x47000000u, 0x7404u | ((unsigned)j << 4)));
+// (`m15` = 0x47000000, handed in as a runtime value -- DScene::m15_bits -- so that the selector is PRMT's immediate)
+LJ_D float byte_to_m15(unsigned w, int j, unsigned m15) {
+    return __uint_as_float(__byte_perm(w, m15, 0x7404u | ((unsigned)j << 4)));
 }
 
 struct Trav8 {
@@ -130,6 +131,7 @@ struct Trav8 {
         const float pz = fmaf(fabsf(cz), 4.76837158e-7f, fabsf(az) * 0.015625f);
         const float c0x = cx - px, c1x = cx + px, c0y = cy - py, c1y = cy + py, c0z = cz - pz, c1z = cz + pz;
         const unsigned oct4 = oct_inv * 0x01010101u;
+        const unsigned m15 = sc.m15_bits;
         unsigned hitmask = 0;
 #pragma unroll
         for (int half = 0; half < 2; half++) {
@@ -148,9 +150,9 @@ struct Trav8 {
             const unsigned bits4 = (meta4 >> 5) & 0x07070707u;                         // 0 for an empty child
 #pragma unroll
             for (int j = 0; j < 4; j++) {
-                const float t0x = fmaf(byte_to_m15(nx, j), ax, c0x), t1x = fmaf(byte_to_m15(fx, j), ax, c1x);
-                const float t0y = fmaf(byte_to_m15(ny, j), ay, c0y), t1y = fmaf(byte_to_m15(fy, j), ay, c1y);
-                const float t0z = fmaf(byte_to_m15(nz, j), az, c0z), t1z = fmaf(byte_to_m15(fz, j), az, c1z);
+                const float t0x = fmaf(byte_to_m15(nx, j, m15), ax, c0x), t1x = fmaf(byte_to_m15(fx, j, m15), ax, c1x);
+                const float t0y = fmaf(byte_to_m15(ny, j, m15), ay, c0y), t1y = fmaf(byte_to_m15(fy, j, m15), ay, c1y);
+                const float t0z = fmaf(byte_to_m15(nz, j, m15), az, c0z), t1z = fmaf(byte_to_m15(fz, j, m15), az, c1z);
                 const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
                 const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, best_t));
                 if (t0 <= t1)

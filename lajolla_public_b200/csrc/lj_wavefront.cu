@@ -12,28 +12,11 @@
 #include "lj_materials.cuh"
 #include "lj_traverse8.cuh"
 #include "lj_wave_common.cuh"
+#include "lj_wf_pool.cuh"
 #include <cstdio>
 #include <cstdlib>
 
 namespace {
-
-enum { Q_EXT = 0, Q_SHADOW = 1, Q_REGEN = 2, Q_FINISH = 3, Q_MISS = 4, Q_KIND0 = 5, Q_COUNT = Q_KIND0 + LJ_MAT_KIND_COUNT };
-
-struct __align__(16) RayRec { double ox, oy, oz, spread, dx, dy, dz, eta_scale; };          // 64 B
-struct __align__(16) ThrRec { double tx, ty, tz, p2, fx, fy, fz; int nv, sample; };          // 64 B
-struct __align__(16) RadRec { double rx, ry, rz; unsigned long long rng; };                  // 32 B
-struct __align__(16) ShadowRec { RayF ray; double cx, cy, cz; int slot, _pad; };             // 64 B
-
-struct WfPool {
-    int capacity, K;
-    long long npix;
-    RayRec *ray; ThrRec *thr; RadRec *rad; HitRec *hit;
-    double *accum;              // 3 per slot
-    ExtRec *ext_ray; int *ext_slot;
-    ShadowRec *shadow;
-    int *q_regen, *q_miss, *q_finish, *q_kind[LJ_MAT_KIND_COUNT];
-    int *counts;                // Q_COUNT live queue sizes
-};
 
 LJ_D void terminate_path(const WfPool &wp, int slot, d3 radiance) {
     double *a = wp.accum + 3 * (size_t)slot;
@@ -71,95 +54,6 @@ __global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n
         wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
         push_extend(wp, slot, ray);
     }
-}
-
-// ---- persistent trace kernels ----
-// Rays differ a lot in traversal length, so a warp that just walks its 32 rays to the end runs
-// mostly empty.  Instead every warp pulls rays from the queue through one atomic work counter
-// and, whenever fewer than REFILL_BELOW lanes are still traversing, hands the idle lanes new
-// rays (warp-aggregated fetch) before stepping on.
-enum { W_EXT = 24, W_SHADOW = 25 };     // work counters inside wp.counts
-
-// ---- stage: extend = rtcIntersect1 (intersection.cpp:32) + classification by material kind ----
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
-    const int n = min(n_upper, wp.counts[Q_EXT]);
-    int ray_idx = -1; bool exhausted = false;
-    Trav8 tv;
-    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
-    unsigned nn = 0, np = 0;
-    while (true) {
-        // retire finished lanes together (the hit reconstruction runs with as many lanes as possible)
-        if (ray_idx >= 0 && !tv.active()) {
-            const int slot = wp.ext_slot[ray_idx];
-            Hit h; HitRec hr; int q;
-            if (tv.finish(sc, &h)) {
-                hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
-                q = Q_KIND0 + sc.materials[sc.shapes[h.geom].material_id].kind;
-            } else {
-                hr.t = 0; hr.u = hr.v = 0; hr.geom = -1; hr.prim = -1; hr.ngx = hr.ngy = hr.ngz = 0;
-                q = Q_MISS;
-            }
-            wp.hit[slot] = hr;
-            int *queue = (q == Q_MISS) ? wp.q_miss : wp.q_kind[q - Q_KIND0];
-            queue[queue_push_pos(&wp.counts[q])] = slot;
-            if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
-            ray_idx = -1;
-        }
-        if (warp_fetch<false>(&wp.counts[W_EXT], n, ray_idx, exhausted)) tv.init(wp.ext_ray[ray_idx].ray);
-        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
-        const int stop_below = exhausted ? 1 : tune.refill_below;
-        while (true) {
-            const bool live = ray_idx >= 0;
-            const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
-            const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
-            if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
-                bool found = false;
-                if (wpr) tv.prim_step<false, COUNT>(sc, found);
-            } else if (mn != 0u) {
-                if (wn) tv.node_step<false, COUNT>(sc);
-            }
-            if (__popc(__ballot_sync(0xffffffffu, live && tv.active())) < stop_below) break;
-        }
-    }
-    if (COUNT) { atomicAdd(&trav_counters[0], (unsigned long long)nn); atomicAdd(&trav_counters[1], (unsigned long long)np); }
-}
-
-// ---- stage: shadow = rtcOccluded1 (intersection.cpp:83) + accumulate the NEE term ----
-template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_shadow(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
-    const int n = min(n_upper, wp.counts[Q_SHADOW]);
-    int ray_idx = -1; bool exhausted = false;
-    Trav8 tv;
-    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
-    bool found = false;
-    unsigned nn = 0, np = 0;
-    while (true) {
-        if (ray_idx >= 0 && (found || !tv.active())) {
-            if (!found) {
-                const ShadowRec *s = &wp.shadow[ray_idx];
-                RadRec *ra = &wp.rad[s->slot];
-                ra->rx += s->cx; ra->ry += s->cy; ra->rz += s->cz;        // path_tracing.h:207
-            }
-            if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
-            ray_idx = -1;
-        }
-        if (warp_fetch<true>(&wp.counts[W_SHADOW], n, ray_idx, exhausted)) { tv.init(wp.shadow[ray_idx].ray); found = false; }
-        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
-        const int stop_below = exhausted ? 1 : tune.refill_below;
-        while (true) {
-            const bool live = ray_idx >= 0 && !found;
-            const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
-            const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
-            if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
-                if (wpr) tv.prim_step<true, COUNT>(sc, found);
-            } else if (mn != 0u) {
-                if (wn) { if (tv.node_step<true, COUNT>(sc)) found = true; }
-            }
-            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0 && !found && tv.active())) < stop_below) break;
-        }
-    }
-    if (COUNT) { atomicAdd(&trav_counters[2], (unsigned long long)nn); atomicAdd(&trav_counters[3], (unsigned long long)np); }
 }
 
 // ---- stage: finish = accumulate paths whose last NEE term had to wait for the shadow stage ----
@@ -467,8 +361,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         k_wf_reset<<<1, 32>>>(wp.counts, Q_REGEN, -1, -1);
         if (stage_timing) cudaEventRecord(ev[1]);
         int ext_upper = n_ext + n_regen;
-        if (counting) k_wf_extend<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_ext);
-        else k_wf_extend<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_ext);
+        lj_wf_launch_extend(d, wp, ext_upper, trav, tune_ext, counting, grid_for(ext_upper, trace_grid_cap));
         k_wf_reset<<<1, 32>>>(wp.counts, Q_EXT, -1, -1);
         if (stage_timing) cudaEventRecord(ev[2]);
         if (kind_present[0]) launch_shade<0>(d, wp, ext_upper, shade_grid_cap);
@@ -482,8 +375,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         if (kind_present[8]) launch_shade<8>(d, wp, ext_upper, shade_grid_cap);
         k_wf_miss<<<grid_for(ext_upper, shade_grid_cap), 128>>>(d, wp, ext_upper);
         if (stage_timing) cudaEventRecord(ev[3]);
-        if (counting) k_wf_shadow<true><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_sh);
-        else k_wf_shadow<false><<<grid_for(ext_upper, trace_grid_cap), 128>>>(d, wp, ext_upper, trav, tune_sh);
+        lj_wf_launch_shadow(d, wp, ext_upper, trav, tune_sh, counting, grid_for(ext_upper, trace_grid_cap));
         k_wf_finish<<<grid_for(ext_upper, shade_grid_cap), 128>>>(wp, ext_upper);
         if (stage_timing) cudaEventRecord(ev[4]);
         // one readback per iteration: queue sizes for the next one (also the ray counts)

@@ -1,0 +1,104 @@
+// The two persistent trace kernels of the wavefront path tracer (stages "extend" and "shadow" of lj_wavefront.cu).
+#include "lj_internal.h"
+#include "lj_wf_pool.cuh"
+
+namespace {
+
+// ---- persistent trace kernels ----
+// Rays differ a lot in traversal length, so a warp that just walks its 32 rays to the end runs
+// mostly empty.  Instead every warp pulls rays from the queue through one atomic work counter
+// and, whenever fewer than REFILL_BELOW lanes are still traversing, hands the idle lanes new
+// rays (warp-aggregated fetch) before stepping on.
+
+// ---- stage: extend = rtcIntersect1 (intersection.cpp:32) + classification by material kind ----
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
+    const int n = min(n_upper, wp.counts[Q_EXT]);
+    int ray_idx = -1; bool exhausted = false;
+    Trav8 tv;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
+    unsigned nn = 0, np = 0;
+    while (true) {
+        // retire finished lanes together (the hit reconstruction runs with as many lanes as possible)
+        if (ray_idx >= 0 && !tv.active()) {
+            const int slot = wp.ext_slot[ray_idx];
+            Hit h; HitRec hr; int q;
+            if (tv.finish(sc, &h)) {
+                hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
+                q = Q_KIND0 + sc.materials[sc.shapes[h.geom].material_id].kind;
+            } else {
+                hr.t = 0; hr.u = hr.v = 0; hr.geom = -1; hr.prim = -1; hr.ngx = hr.ngy = hr.ngz = 0;
+                q = Q_MISS;
+            }
+            wp.hit[slot] = hr;
+            int *queue = (q == Q_MISS) ? wp.q_miss : wp.q_kind[q - Q_KIND0];
+            queue[queue_push_pos(&wp.counts[q])] = slot;
+            if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
+            ray_idx = -1;
+        }
+        if (warp_fetch<false>(&wp.counts[W_EXT], n, ray_idx, exhausted)) tv.init(wp.ext_ray[ray_idx].ray);
+        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
+        const int stop_below = exhausted ? 1 : tune.refill_below;
+        while (true) {
+            const bool live = ray_idx >= 0;
+            const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
+            const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
+                bool found = false;
+                if (wpr) tv.prim_step<false, COUNT>(sc, found);
+            } else if (mn != 0u) {
+                if (wn) tv.node_step<false, COUNT>(sc);
+            }
+            if (__popc(__ballot_sync(0xffffffffu, live && tv.active())) < stop_below) break;
+        }
+    }
+    if (COUNT) { atomicAdd(&trav_counters[0], (unsigned long long)nn); atomicAdd(&trav_counters[1], (unsigned long long)np); }
+}
+
+// ---- stage: shadow = rtcOccluded1 (intersection.cpp:83) + accumulate the NEE term ----
+template <bool COUNT>
+__global__ void __launch_bounds__(128) k_wf_shadow(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
+    const int n = min(n_upper, wp.counts[Q_SHADOW]);
+    int ray_idx = -1; bool exhausted = false;
+    Trav8 tv;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
+    bool found = false;
+    unsigned nn = 0, np = 0;
+    while (true) {
+        if (ray_idx >= 0 && (found || !tv.active())) {
+            if (!found) {
+                const ShadowRec *s = &wp.shadow[ray_idx];
+                RadRec *ra = &wp.rad[s->slot];
+                ra->rx += s->cx; ra->ry += s->cy; ra->rz += s->cz;        // path_tracing.h:207
+            }
+            if (COUNT) { nn += tv.n_nodes; np += tv.n_prims; }
+            ray_idx = -1;
+        }
+        if (warp_fetch<true>(&wp.counts[W_SHADOW], n, ray_idx, exhausted)) { tv.init(wp.shadow[ray_idx].ray); found = false; }
+        if (!__ballot_sync(0xffffffffu, ray_idx >= 0)) break;
+        const int stop_below = exhausted ? 1 : tune.refill_below;
+        while (true) {
+            const bool live = ray_idx >= 0 && !found;
+            const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
+            const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
+                if (wpr) tv.prim_step<true, COUNT>(sc, found);
+            } else if (mn != 0u) {
+                if (wn) { if (tv.node_step<true, COUNT>(sc)) found = true; }
+            }
+            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0 && !found && tv.active())) < stop_below) break;
+        }
+    }
+    if (COUNT) { atomicAdd(&trav_counters[2], (unsigned long long)nn); atomicAdd(&trav_counters[3], (unsigned long long)np); }
+}
+
+}  // namespace
+
+void lj_wf_launch_extend(const DScene &sc, const WfPool &wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune, bool counting, unsigned grid) {
+    if (counting) k_wf_extend<true><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
+    else k_wf_extend<false><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
+}
+void lj_wf_launch_shadow(const DScene &sc, const WfPool &wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune, bool counting, unsigned grid) {
+    if (counting) k_wf_shadow<true><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
+    else k_wf_shadow<false><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
+}

@@ -159,6 +159,8 @@ def test_every_reference_obj_matches(gpu, xf):
         text = open(path, "rb").read()
         got = gpu.load_obj(text, ref["to_world"], ref["to_local"])
         check_mesh(got, ref, not _faces_use_vn(text), f"{rel} {xf}")
+        if len(text) > 100000:
+            print(f"{rel}: {len(text)} bytes, {len(ref['positions'])} vertices, {len(ref['indices'])} triangles, device decode {got['decode_ms']:.3f} ms")
     print(f"{len(files)} obj files match the reference's parse_obj ({xf} to_world)")
 
 
