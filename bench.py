@@ -290,7 +290,10 @@ def roofline_block(scene, rp, stage, rays_by_type, iterations, peak, which, scra
     step_ms = sum(stage.values())
     traffic = None
     try:   # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel (profiles/)
-        traffic = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_wf_extend<0>"]["dram_bytes_per_launch"]
+        # (the captured launch is an early, larger one: its bytes are scaled to the average launch by the ratio of the
+        #  launch-list average duration to the captured launch's duration -- tools/summarize_profiles.py)
+        t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_wf_extend<0>"]
+        traffic = t.get("dram_bytes_per_avg_launch", t["dram_bytes_per_launch"])
     except Exception:
         pass
     return {"bound": "hbm", "kernel": "k_wf_extend<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",

@@ -33,7 +33,7 @@ __global__ void k_collapse_level(const Work *items, int n_items, Work *items_out
                                  const int *left, const int *right, const float4 *node_lo, const float4 *node_hi,
                                  const int *count, const int *sorted_prim,
                                  const float4 *prim_lo, const float4 *prim_hi, const float4 *tri_verts,
-                                 Bvh8Node *nodes8, int *node_counter, float4 *tri_verts8, int *prim_counter, int n_prims_total, int MAX_LEAF) {
+                                 Bvh8Node *nodes8, int *node_counter, float4 *tri_verts8, int *prim_counter, int n_prims_total, int MAX_LEAF, int open_leaves) {
     int wi = blockIdx.x * blockDim.x + threadIdx.x;
     if (wi >= n_items) return;
     Work w = items[wi];
@@ -53,6 +53,24 @@ __global__ void k_collapse_level(const Work *items, int n_items, Work *items_out
         for (int i = 0; i < nchild; i++) {
             int c = child[i];
             if (c < 0 || child_count(c, count) <= MAX_LEAF) continue;
+            float4 l = node_lo[c], h = node_hi[c];
+            float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z;
+            float a = dx * dy + dy * dz + dz * dx;
+            if (a > best_area) { best_area = a; best = i; }
+        }
+        if (best < 0) break;
+        int c = child[best];
+        child[best] = left[c];
+        child[nchild++] = right[c];
+    }
+    // Slots left over (the bottom of the tree: every child already holds <= MAX_LEAF primitives): split multi-primitive
+    // leaf children as well, largest box first, so that each primitive (or pair) gets its own, tighter child box.  Same
+    // number of nodes, fewer primitive tests.
+    while (open_leaves && nchild < 8) {
+        int best = -1; float best_area = -1.f;
+        for (int i = 0; i < nchild; i++) {
+            int c = child[i];
+            if (c < 0) continue;
             float4 l = node_lo[c], h = node_hi[c];
             float dx = h.x - l.x, dy = h.y - l.y, dz = h.z - l.z;
             float a = dx * dy + dy * dz + dz * dx;
@@ -184,13 +202,15 @@ int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left,
     CK(cudaMemcpy(q0, &root, sizeof root, cudaMemcpyHostToDevice));
     int max_leaf = MAX_LEAF_CAP;      // LJ_MAX_LEAF: experiment knob (1..3)
     if (const char *e = getenv("LJ_MAX_LEAF")) { int v = atoi(e); if (v >= 1 && v <= MAX_LEAF_CAP) max_leaf = v; }
+    int open_leaves = 1;              // LJ_OPEN_LEAVES=0: experiment knob
+    if (const char *e = getenv("LJ_OPEN_LEAVES")) open_leaves = atoi(e) != 0;
     int n_items = 1;
     int levels = 0;
     while (n_items > 0) {
         CK(cudaMemset(counters + 2, 0, sizeof(int)));
         k_collapse_level<<<(n_items + 63) / 64, 64>>>(q0, n_items, q1, counters + 2, left, right, node_lo, node_hi,
                                                        count, sorted_prim, prim_lo, prim_hi, tri_verts,
-                                                       out.bvh8, counters, out.tri_verts8, counters + 1, n, max_leaf);
+                                                       out.bvh8, counters, out.tri_verts8, counters + 1, n, max_leaf, open_leaves);
         CK(cudaGetLastError());
         CK(cudaMemcpy(h_counters, counters, sizeof h_counters, cudaMemcpyDeviceToHost));
         n_items = h_counters[2];

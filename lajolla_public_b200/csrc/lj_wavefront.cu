@@ -334,8 +334,8 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     int trace_grid_cap = sm * 16; const int shade_grid_cap = sm * 16;
     auto env_int = [](const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; };
     TraceTuning tune_ext, tune_sh;     // tuning knobs (defaults measured on B200, see profiles/)
-    tune_ext.refill_below = env_int("LJ_REFILL_BELOW", 24); tune_ext.prim_thresh = env_int("LJ_PRIM_THRESH", 8);
-    tune_sh.refill_below = env_int("LJ_REFILL_BELOW_SHADOW", 24); tune_sh.prim_thresh = env_int("LJ_PRIM_THRESH_SHADOW", 4);
+    tune_ext.refill_below = env_int("LJ_REFILL_BELOW", 24); tune_ext.prim_thresh = env_int("LJ_PRIM_THRESH", 12);
+    tune_sh.refill_below = env_int("LJ_REFILL_BELOW_SHADOW", 24); tune_sh.prim_thresh = env_int("LJ_PRIM_THRESH_SHADOW", 6);
     const int trace_mult = env_int("LJ_TRACE_GRID_MULT", 16);
     trace_grid_cap = sm * trace_mult;
     const bool trace_iters = getenv("LJ_WF_TRACE") != nullptr;

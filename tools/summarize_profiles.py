@@ -35,6 +35,7 @@ KEYS = [
 
 
 TRAFFIC = {}
+LIST_AVG_MS = {}     # kernel -> average launch duration in the launch list (same serialised, cold-cache conditions as a full capture)
 
 
 def short(name):
@@ -54,6 +55,8 @@ def launches(tag, src, out):
     for r in rows[1:]:
         n = short(r[k]); tot[n] += float(r[v].replace(",", "")) * 1e-6; cnt[n] += 1
     total = sum(tot.values())
+    for n in tot:
+        LIST_AVG_MS[n] = tot[n] / cnt[n]
     with open(os.path.join(out, f"{tag}_launches.md"), "w") as f:
         f.write(f"# {tag}: ncu launch list of `python bench.py --steps 1 --warmup 1 --no-cpu-baseline`\n\n")
         f.write("`ncu --metrics gpu__time_duration.sum --clock-control none` (per-launch times are serialised and "
@@ -110,6 +113,12 @@ def main():
     os.makedirs(out, exist_ok=True)
     launches(tag, src, out)
     full(tag, src, out)
+    for k, t in TRAFFIC.items():
+        # the captured launch is one of the early, larger ones; the launch list gives the duration of the average
+        # launch under the same conditions, so bench.py can scale the capture's DRAM bytes to an average launch
+        if k in LIST_AVG_MS:
+            t["launch_list_avg_ms"] = LIST_AVG_MS[k]
+            t["dram_bytes_per_avg_launch"] = t["dram_bytes_per_launch"] * LIST_AVG_MS[k] / t["launch_ms"]
     if TRAFFIC:
         json.dump(TRAFFIC, open(os.path.join(out, "traffic.json"), "w"), indent=1)
     lines = {}
