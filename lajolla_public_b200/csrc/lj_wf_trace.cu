@@ -2,6 +2,12 @@
 #include "lj_internal.h"
 #include "lj_wf_pool.cuh"
 
+// resident blocks per SM the trace kernels are compiled for (register budget = 65536 / (128 * this)).  Measured on
+// sponza (extend stage): 5 -> 111 ms, 6 -> 105, 8 -> 95.3, 9 -> 93.2, 10 (48 registers, 60-84 B of spills) -> 91.5, 11 / 12 -> 100.5.
+#ifndef LJ_TRACE_MIN_BLOCKS
+#define LJ_TRACE_MIN_BLOCKS 10
+#endif
+
 namespace {
 
 // ---- persistent trace kernels ----
@@ -12,7 +18,7 @@ namespace {
 
 // ---- stage: extend = rtcIntersect1 (intersection.cpp:32) + classification by material kind ----
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
+__global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
     const int n = min(n_upper, wp.counts[Q_EXT]);
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
@@ -57,7 +63,7 @@ __global__ void __launch_bounds__(128) k_wf_extend(DScene sc, WfPool wp, int n_u
 
 // ---- stage: shadow = rtcOccluded1 (intersection.cpp:83) + accumulate the NEE term ----
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_wf_shadow(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
+__global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_shadow(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
     const int n = min(n_upper, wp.counts[Q_SHADOW]);
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
