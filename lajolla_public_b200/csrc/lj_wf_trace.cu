@@ -49,13 +49,13 @@ __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_extend(DScene s
             const bool live = ray_idx >= 0;
             const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
             const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (__popc(mn | mp) < stop_below) break;          // too few lanes still traversing: retire + refill first
             if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
                 bool found = false;
                 if (wpr) tv.prim_step<false, COUNT>(sc, found);
-            } else if (mn != 0u) {
+            } else {
                 if (wn) tv.node_step<false, COUNT>(sc);
             }
-            if (__popc(__ballot_sync(0xffffffffu, live && tv.active())) < stop_below) break;
         }
     }
     if (COUNT) { atomicAdd(&trav_counters[0], (unsigned long long)nn); atomicAdd(&trav_counters[1], (unsigned long long)np); }
@@ -87,12 +87,12 @@ __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_shadow(DScene s
             const bool live = ray_idx >= 0 && !found;
             const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
             const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (__popc(mn | mp) < stop_below) break;
             if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
                 if (wpr) tv.prim_step<true, COUNT>(sc, found);
-            } else if (mn != 0u) {
+            } else {
                 if (wn) { if (tv.node_step<true, COUNT>(sc)) found = true; }
             }
-            if (__popc(__ballot_sync(0xffffffffu, ray_idx >= 0 && !found && tv.active())) < stop_below) break;
         }
     }
     if (COUNT) { atomicAdd(&trav_counters[2], (unsigned long long)nn); atomicAdd(&trav_counters[3], (unsigned long long)np); }
