@@ -101,7 +101,9 @@ struct Trav8 {
     // Node phase: open one pending inner child and slab-test its 8 children.  Inner hits become
     // the new node group; leaf hits become a primitive group, held in `tg` or postponed on the stack.
     // Requires wants_node().  Returns true only if an occluder was found (ANY, stack-overflow path).
-    template <bool ANY, bool COUNT>
+    // REFILL = false: the caller pulls from the stack itself (the wavefront trace loops do it once per iteration with
+    // all lanes converged, instead of inside the divergent tail of each phase).
+    template <bool ANY, bool COUNT, bool REFILL = true>
     LJ_D bool node_step(const DScene &sc) {
         const int bit = 31 - __clz(ng.y);
         ng.y &= ~(1u << bit);
@@ -155,8 +157,8 @@ struct Trav8 {
                 const float t0z = fmaf(byte_to_m15(nz, j, m15), az, c0z), t1z = fmaf(byte_to_m15(fz, j, m15), az, c1z);
                 const float t0 = fmaxf(fmaxf(t0x, t0y), fmaxf(t0z, r.tnear));
                 const float t1 = fminf(fminf(t1x, t1y), fminf(t1z, best_t));
-                if (t0 <= t1)
-                    hitmask |= byte_of(bits4, j) << byte_of(index4, j);
+                if (t0 <= t1)      // one PRMT extracts the byte; the shift uses the low 5 bits of the index byte
+                    hitmask |= __byte_perm(bits4, 0u, 0x4440u + j) << byte_of(index4, j);
             }
         }
         ng = make_uint2(__float_as_uint(n1.x), (hitmask & 0xff000000u) | (ew >> 24));
@@ -173,19 +175,19 @@ struct Trav8 {
                 }
             }
         }
-        refill_from_stack();
+        if (REFILL) refill_from_stack();
         return false;
     }
 
     // Primitive phase: test ONE pending primitive of `tg`.  Requires wants_prim().  Returns true
     // when an occluder was found (ANY only).
-    template <bool ANY, bool COUNT>
+    template <bool ANY, bool COUNT, bool REFILL = true>
     LJ_D bool prim_step(const DScene &sc, bool &found) {
         const int b = __ffs(tg.y) - 1;
         tg.y &= tg.y - 1;
         if (COUNT) n_prims++;
         if (prim<ANY>(sc, (int)tg.x + b)) { found = true; return true; }
-        if (tg.y == 0u) refill_from_stack();
+        if (REFILL && tg.y == 0u) refill_from_stack();
         return false;
     }
 

@@ -4,6 +4,18 @@
 
 // resident blocks per SM the trace kernels are compiled for (register budget = 65536 / (128 * this)).  Measured on
 // sponza (extend stage): 5 -> 111 ms, 6 -> 105, 8 -> 95.3, 9 -> 93.2, 10 (48 registers, 60-84 B of spills) -> 91.5, 11 / 12 -> 100.5.
+#ifndef LJ_PRIMS_PER_PHASE
+#define LJ_PRIMS_PER_PHASE 2
+#endif
+#ifndef LJ_PRIMS_PER_PHASE_SHADOW
+#define LJ_PRIMS_PER_PHASE_SHADOW 1
+#endif
+#ifndef LJ_NODES_PER_PHASE
+#define LJ_NODES_PER_PHASE 1
+#endif
+#ifndef LJ_REFILL_TOP
+#define LJ_REFILL_TOP 0
+#endif
 #ifndef LJ_TRACE_MIN_BLOCKS
 #define LJ_TRACE_MIN_BLOCKS 10
 #endif
@@ -47,14 +59,29 @@ __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_extend(DScene s
         const int stop_below = exhausted ? 1 : tune.refill_below;
         while (true) {
             const bool live = ray_idx >= 0;
+#if LJ_REFILL_TOP
+            if (live) tv.refill_from_stack();
+#endif
             const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
             const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
             if (__popc(mn | mp) < stop_below) break;          // too few lanes still traversing: retire + refill first
             if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
                 bool found = false;
-                if (wpr) tv.prim_step<false, COUNT>(sc, found);
+                if (wpr) {
+                    tv.prim_step<false, COUNT, !LJ_REFILL_TOP>(sc, found);
+#if LJ_PRIMS_PER_PHASE > 1
+#pragma unroll 1
+                    for (int k = 1; k < LJ_PRIMS_PER_PHASE && tv.wants_prim(); k++) tv.prim_step<false, COUNT, !LJ_REFILL_TOP>(sc, found);
+#endif
+                }
             } else {
-                if (wn) tv.node_step<false, COUNT>(sc);
+                if (wn) {
+                    tv.node_step<false, COUNT, !LJ_REFILL_TOP>(sc);
+#if LJ_NODES_PER_PHASE > 1
+#pragma unroll 1
+                    for (int k = 1; k < LJ_NODES_PER_PHASE && tv.wants_node(); k++) tv.node_step<false, COUNT, !LJ_REFILL_TOP>(sc);
+#endif
+                }
             }
         }
     }
@@ -85,13 +112,22 @@ __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_shadow(DScene s
         const int stop_below = exhausted ? 1 : tune.refill_below;
         while (true) {
             const bool live = ray_idx >= 0 && !found;
+#if LJ_REFILL_TOP
+            if (live) tv.refill_from_stack();
+#endif
             const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
             const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
             if (__popc(mn | mp) < stop_below) break;
             if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
-                if (wpr) tv.prim_step<true, COUNT>(sc, found);
+                if (wpr) {
+                    tv.prim_step<true, COUNT, !LJ_REFILL_TOP>(sc, found);
+#if LJ_PRIMS_PER_PHASE_SHADOW > 1
+#pragma unroll 1
+                    for (int k = 1; k < LJ_PRIMS_PER_PHASE_SHADOW && !found && tv.wants_prim(); k++) tv.prim_step<true, COUNT, !LJ_REFILL_TOP>(sc, found);
+#endif
+                }
             } else {
-                if (wn) { if (tv.node_step<true, COUNT>(sc)) found = true; }
+                if (wn) { if (tv.node_step<true, COUNT, !LJ_REFILL_TOP>(sc)) found = true; }
             }
         }
     }
