@@ -119,7 +119,7 @@ def reference_arm(args):
     cores = host_cores()
     probe = run_reference_sample(1, cores)
     if probe is None:
-        print(json.dumps({"impl": "reference", "unavailable": "oracle/_ref/ref_driver or its scene copy is missing (build() in the authoring container creates both)"}))
+        emit(({"impl": "reference", "unavailable": "oracle/_ref/ref_driver or its scene copy is missing (build() in the authoring container creates both)"}))
         return
     # size each step to ~8 s of wall time
     spp = max(1, min(SPP_PER_STEP, int(round(8.0 / max(probe["render_s"], 1e-3)))))
@@ -138,7 +138,7 @@ def reference_arm(args):
             "cpu_baseline": {"value": v, "unit": "Mrays/s", "cores": cores, "kind": "reference",
                              "sample": f"{spp} spp of sponza 768x575 per step, reference sources + BVH shim (not Embree)"},
             "e2e": {"value": v, "unit": "Mrays/s", "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line))
+    emit(line)
 
 
 def gpu_arm(args):
@@ -262,7 +262,7 @@ def gpu_arm(args):
                 line["cpu_baseline"] = {"value": (r["intersect_rays"] + r["occluded_rays"]) / r["render_s"] * 1e-6, "unit": "Mrays/s",
                                         "cores": cores, "kind": "reference", "msamples_per_s": r["msamples_per_s"],
                                         "sample": f"{spp} spp of sponza 768x575 ({r['render_s']:.1f} s), reference sources + BVH shim (not Embree)"}
-        print(json.dumps(line))
+        emit(line)
     scene.close(); gpu.close()
     if world > 1:
         dist.destroy_process_group()
@@ -308,7 +308,20 @@ def roofline_block(scene, rp, stage, rays_by_type, iterations, peak, which, scra
                     "the practical limiter is dependent-load latency + divergence (see profiles/)"}
 
 
+_OUT = None
+
+
+def emit(line):
+    """the ONE JSON line, on the process's real stdout"""
+    print(json.dumps(line), file=_OUT if _OUT is not None else sys.stdout, flush=True)
+
+
 def main():
+    # stdout carries exactly one JSON line: anything libraries print on fd 1 (NCCL's version banner, ...) goes to stderr
+    global _OUT
+    sys.stdout.flush()
+    _OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=3)
