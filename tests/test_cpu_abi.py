@@ -132,3 +132,21 @@ def test_blob_film_override():
     assert (wh[0], wh[1]) == (128, 96)
     assert opt[1] == 7 and opt[0] == 5      # LJ_INTEGRATOR_PATH
     d.close()
+
+
+def test_asset_loaders_reject_null_arguments_without_a_device():
+    """the asset decoders validate their arguments before touching CUDA and have no host decode path:
+    without a context they fail with LJ_EINVAL and a message; the free functions accept an empty record"""
+    from lajolla_public_b200 import load_library
+    from lajolla_public_b200.api import MeshData, VolumeData
+    lib = load_library()
+    m, v = MeshData(), VolumeData()
+    eye = np.eye(4)
+    assert lib.lj_mesh_load_obj(None, b"v 0 0 0\n", 8, eye.ctypes.data, eye.ctypes.data, C.byref(m)) == -1
+    assert b"lj_mesh_load_obj" in lib.lj_last_error()
+    assert lib.lj_mesh_load_serialized(None, b"\x1c\x04\x04\x00", 4, 0, eye.ctypes.data, eye.ctypes.data, C.byref(m)) == -1
+    assert lib.lj_mesh_compute_normals(None, None, 0, None, 0, None) == -1
+    assert lib.lj_volume_load(None, b"VOL\x03", 4, 3, C.byref(v)) == -1
+    assert b"lj_volume_load" in lib.lj_last_error()
+    lib.lj_mesh_free(C.byref(m)); lib.lj_volume_free(C.byref(v))      # zeroed records: no-ops
+    assert not m.positions and not v.data
