@@ -121,7 +121,7 @@ __global__ void __launch_bounds__(128) k_vol_generate(DScene sc, VolPool vp, int
 
 // ---- stage: extend = intersect() for main rays and NEE segments ----
 template <bool COUNT>
-__global__ void __launch_bounds__(128) k_vol_extend(DScene sc, VolPool vp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
+__global__ void __launch_bounds__(128, 10) k_vol_extend(DScene sc, VolPool vp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
     const int n = min(n_upper, vp.counts[VQ_EXT]);
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
@@ -151,13 +151,16 @@ __global__ void __launch_bounds__(128) k_vol_extend(DScene sc, VolPool vp, int n
             const bool live = ray_idx >= 0;
             const bool wn = live && tv.wants_node(), wpr = live && tv.wants_prim();
             const unsigned mn = __ballot_sync(0xffffffffu, wn), mp = __ballot_sync(0xffffffffu, wpr);
+            if (__popc(mn | mp) < stop_below) break;          // same loop as k_wf_extend (lj_wf_trace.cu)
             if (mp != 0u && (__popc(mp) >= tune.prim_thresh || mn == 0u)) {
                 bool found = false;
-                if (wpr) tv.prim_step<false, COUNT>(sc, found);
-            } else if (mn != 0u) {
+                if (wpr) {
+                    tv.prim_step<false, COUNT>(sc, found);
+                    if (tv.wants_prim()) tv.prim_step<false, COUNT>(sc, found);
+                }
+            } else {
                 if (wn) tv.node_step<false, COUNT>(sc);
             }
-            if (__popc(__ballot_sync(0xffffffffu, live && tv.active())) < stop_below) break;
         }
     }
     if (COUNT) { atomicAdd(&trav_counters[0], (unsigned long long)nn); atomicAdd(&trav_counters[1], (unsigned long long)np); }
