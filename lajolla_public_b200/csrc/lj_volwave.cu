@@ -21,6 +21,14 @@
 #include <cstdlib>
 #include <algorithm>
 
+// resident blocks per SM the per-vertex and tracking kernels are compiled for (experiment knobs; 1 = no register cap)
+#ifndef LJ_VOL_TRACK_MIN_BLOCKS
+#define LJ_VOL_TRACK_MIN_BLOCKS 1
+#endif
+#ifndef LJ_VOL_MAIN_MIN_BLOCKS
+#define LJ_VOL_MAIN_MIN_BLOCKS 1
+#endif
+
 namespace {
 
 enum { VQ_EXT = 0, VQ_REGEN = 1, VQ_MAIN = 2, VQ_NEE = 3, VQ_FIN_MEDIUM = 4, VQ_FIN_KIND0 = 5,
@@ -205,7 +213,7 @@ LJ_D int tracked_medium(const DScene &sc, int medium) {
 }
 
 template <bool NEE>
-__global__ void __launch_bounds__(128) k_vol_track(DScene sc, VolPool vp, int n_upper, int refill_below, int budget, int min_items, int parity) {
+__global__ void __launch_bounds__(128, LJ_VOL_TRACK_MIN_BLOCKS) k_vol_track(DScene sc, VolPool vp, int n_upper, int refill_below, int budget, int min_items, int parity) {
     // work = the segments suspended by the previous launch, then the fresh ones from the extend stage
     const int *q_cont = NEE ? vp.q_cont_nee[parity] : vp.q_cont_main[parity];
     int *q_susp = NEE ? vp.q_cont_nee[parity ^ 1] : vp.q_cont_main[parity ^ 1];
@@ -292,7 +300,7 @@ __global__ void __launch_bounds__(128) k_vol_track(DScene sc, VolPool vp, int n_
 }
 
 // ---- stage: main (vol_path_tracing.h:543-760 up to the light sample of the NEE, :311-320) ----
-__global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_upper, const int *queue, int count_idx) {
+__global__ void __launch_bounds__(128, LJ_VOL_MAIN_MIN_BLOCKS) k_vol_main(DScene sc, VolPool vp, int n_upper, const int *queue, int count_idx) {
     const int n = min(n_upper, vp.counts[count_idx]);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned together = __activemask();
@@ -399,7 +407,7 @@ __global__ void __launch_bounds__(128) k_vol_main(DScene sc, VolPool vp, int n_u
 }
 
 // ---- stage: nee = one segment of next_event_estimation_final's loop (:335-439) ----
-__global__ void __launch_bounds__(128) k_vol_nee(DScene sc, VolPool vp, int n_upper, const int *queue, int count_idx) {
+__global__ void __launch_bounds__(128, LJ_VOL_MAIN_MIN_BLOCKS) k_vol_nee(DScene sc, VolPool vp, int n_upper, const int *queue, int count_idx) {
     const int n = min(n_upper, vp.counts[count_idx]);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         const unsigned together = __activemask();
