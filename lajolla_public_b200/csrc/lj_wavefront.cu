@@ -312,8 +312,9 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     if (!d.bvh8) return lj_render_megakernel(s, rl, dev_sum, st);   // LJ_BVH=2 validation mode: binary tree only
     const long long npix = (long long)rl.width * rl.height;
     const int nsamp = rl.s_end - rl.s_begin;
-    // pool sizing: K slots per pixel, ~2M paths in flight unless the caller says otherwise
-    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (4LL << 20);
+    // pool sizing: K slots per pixel, ~8 Mi paths in flight unless the caller says otherwise (sweep 2..16 Mi in
+    // profiles/r01_experiments.md: fewer, larger iterations; sponza is flat from 4 Mi, matpreview gains 13 %)
+    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (8LL << 20);
     int K = (int)((target + npix - 1) / npix);
     if (K > nsamp) K = nsamp;
     if (K < 1) K = 1;
