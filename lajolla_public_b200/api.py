@@ -167,8 +167,8 @@ class LajollaGPU:
         _check(self.lib, self.lib.lj_init(int(device), C.byref(self.handle)), "lj_init")
         self.device = device
 
-    def load_scene(self, blob_path, res=None, spp=None):
-        return Scene(self, blob_path, res=res, spp=spp)
+    def load_scene(self, blob_path, res=None, spp=None, integrator=None):
+        return Scene(self, blob_path, res=res, spp=spp, integrator=integrator)
 
     def scene_from_desc(self, desc, flags=0):
         return Scene(self, desc=desc, flags=flags)
@@ -277,7 +277,7 @@ IMAGE_PFM, IMAGE_EXR = 0, 1
 class HostSceneDesc:
     """A flattened scene held in HOST memory (lj_scene_desc_load); optionally page-locked."""
 
-    def __init__(self, blob_path, pin=False, res=None, spp=None):
+    def __init__(self, blob_path, pin=False, res=None, spp=None, integrator=None):
         self.lib = load_library()
         self.handle = C.c_void_p()
         _check(self.lib, self.lib.lj_scene_desc_load(os.fsencode(blob_path), C.byref(self.handle)), "lj_scene_desc_load")
@@ -288,6 +288,9 @@ class HostSceneDesc:
         if spp is not None:   # lj_options.samples_per_pixel
             opt = (C.c_int32 * 6).from_address(self.handle.value + 280)
             opt[1] = int(spp)
+        if integrator is not None:   # lj_options.integrator (LJ_INTEGRATOR_*): what parse_scene.cpp:256-304 selects
+            opt = (C.c_int32 * 6).from_address(self.handle.value + 280)
+            opt[0] = int(integrator)
         self.pinned = bool(pin) and self.lib.lj_scene_desc_pin(self.handle, 1) == 0
 
     def _u64(self, off):
@@ -318,12 +321,12 @@ class HostSceneDesc:
 class Scene:
     """A flattened scene blob (.ljs, written by bin/lj_flatten or LJ_SAVE_SCENE) resident on the GPU."""
 
-    def __init__(self, gpu, blob_path=None, res=None, spp=None, desc=None, flags=0):
+    def __init__(self, gpu, blob_path=None, res=None, spp=None, desc=None, flags=0, integrator=None):
         self.gpu = gpu
         lib = gpu.lib
         own = desc is None
         if own:
-            desc = HostSceneDesc(blob_path, res=res, spp=spp)
+            desc = HostSceneDesc(blob_path, res=res, spp=spp, integrator=integrator)
         self.handle = C.c_void_p()
         try:
             if flags:

@@ -445,9 +445,15 @@ RTC_API void rtcGetSceneBounds(RTCScene s_, struct RTCBounds *b) {
     b->upper_x = s->hi[0]; b->upper_y = s->hi[1]; b->upper_z = s->hi[2]; b->align1 = 0;
 }
 
+// What the calling thread's last rtcIntersect1 returned (the seam dump of ref_driver reads the raw f32
+// tfar / u / v / Ng that the reference's PathVertex no longer carries).
+static thread_local RTCRayHit g_last_rayhit;
+extern "C" void lj_shim_last_rayhit(RTCRayHit *out) { *out = g_last_rayhit; }
+
 RTC_API void rtcIntersect1(RTCScene s, struct RTCIntersectContext *ctx, struct RTCRayHit *rh) {
     my_counter()->isect.fetch_add(1, std::memory_order_relaxed);
     traverse<false>((SceneImpl *)s, ctx, rh->ray, &rh->hit);
+    g_last_rayhit = *rh;
 }
 RTC_API void rtcOccluded1(RTCScene s, struct RTCIntersectContext *ctx, struct RTCRay *ray) {
     my_counter()->occl.fetch_add(1, std::memory_order_relaxed);

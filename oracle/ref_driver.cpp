@@ -16,10 +16,10 @@
 //                the reference path by path without serialising a tile.
 //       --res W H overrides the film size only (camera matrices untouched); used to
 //       mint small goldens.  The same override exists in lj_flatten.
-//   ref_driver hits <scene.xml> -o hits.bin
-//       primary-ray closest hits through the reference's intersect() for the
-//       pixel-centre ray of every pixel (aux_render's ray, render.cpp:27):
-//       per pixel {float t,u,v; int geomID, primID} with t = distance.
+//   ref_driver hits <scene.xml> -o hits.bin [--res W H]
+//       ray-cast seam dump: per pixel a primary, a bounce and a shadow ray as f32 (what the
+//       reference hands to Embree) with the results of the reference's intersect() / occluded()
+//       (format: see cmd_hits).
 //   ref_driver imwrite <in.f32img> <out.pfm|out.exr>
 //       the reference's imwrite() (image.cpp:135-173) applied to a raw image
 //       {int32 w, h; float rgb[h][w][3]} (widened to the Image3 doubles imwrite takes):
@@ -153,31 +153,109 @@ static int cmd_render(int argc, char **argv) {
     return 0;
 }
 
+// Seam dump (rtcIntersect1 / rtcOccluded1 as the reference reaches them): three ray sets per pixel, each stored as
+// the f32 ray the reference hands to Embree (the casts of intersection.cpp:15-24 / :71-78) plus what came back
+// through the reference's own intersect() / occluded():
+//   primary : the pixel-centre camera ray (aux_render's ray, render.cpp:27)
+//   bounce  : from the primary hit, a direction drawn from a per-pixel pcg32 stream in the hemisphere of the
+//             geometric normal, tnear = eps, tfar = inf (the shape of path_tracing.h:237's bsdf ray): incoherent
+//   shadow  : from the primary hit towards a light sample drawn like path_tracing.h:97-127 (sample_light,
+//             sample_point_on_light, tnear = eps, tfar = (1-eps) dist; envmap: tfar = inf), through occluded()
+// File: {int32 w, h, version = 3, n_sets = 3} then per set w*h records
+//   {float org[3], tnear, dir[3], tfar;  float t, u, v; int32 geomID, primID; float Ng[3];  int32 valid, occluded}
+// t, u, v, Ng are the raw RTCRayHit values of that intersect() call (read back from the shim, and cross-checked here
+// against the PathVertex the reference built from them).  valid = 0: no ray for this pixel (the primary ray
+// missed).  For the shadow set only `occluded` is meaningful.
+extern "C" void lj_shim_last_rayhit(RTCRayHit *out);
+struct SeamRec {
+    float org[3], tnear, dir[3], tfar;
+    float t, u, v; int geom, prim; float ng[3];
+    int valid, occl;
+};
+static long g_seam_mismatch = 0;
+static void seam_set_ray(SeamRec &r, const Ray &ray) {
+    r.org[0] = (float)ray.org[0]; r.org[1] = (float)ray.org[1]; r.org[2] = (float)ray.org[2];
+    r.dir[0] = (float)ray.dir[0]; r.dir[1] = (float)ray.dir[1]; r.dir[2] = (float)ray.dir[2];
+    r.tnear = (float)ray.tnear; r.tfar = (float)ray.tfar; r.valid = 1;
+}
+static void seam_set_hit(SeamRec &r, const Ray &ray, const std::optional<PathVertex> &v) {
+    if (!v) return;
+    RTCRayHit rh; lj_shim_last_rayhit(&rh);
+    r.t = rh.ray.tfar; r.u = rh.hit.u; r.v = rh.hit.v; r.geom = (int)rh.hit.geomID; r.prim = (int)rh.hit.primID;
+    r.ng[0] = rh.hit.Ng_x; r.ng[1] = rh.hit.Ng_y; r.ng[2] = rh.hit.Ng_z;
+    // the vertex the reference built must come from exactly these values (intersection.cpp:38-48)
+    Vector3 p = ray.org + ray.dir * Real(rh.ray.tfar);
+    if (r.geom != v->shape_id || r.prim != v->primitive_id || Real(r.u) != v->st[0] || Real(r.v) != v->st[1] ||
+        p[0] != v->position[0] || p[1] != v->position[1] || p[2] != v->position[2]) g_seam_mismatch++;
+}
+
 static int cmd_hits(int argc, char **argv) {
     std::string scene_file, out = "hits.bin";
-    for (int i = 2; i < argc; i++) { std::string a = argv[i]; if (a == "-o") out = argv[++i]; else scene_file = a; }
+    int res_w = 0, res_h = 0;
+    for (int i = 2; i < argc; i++) {
+        std::string a = argv[i];
+        if (a == "-o") out = argv[++i];
+        else if (a == "--res") { res_w = atoi(argv[++i]); res_h = atoi(argv[++i]); }
+        else scene_file = a;
+    }
     char cwd[4096]; if (!getcwd(cwd, sizeof cwd)) return 2;
     if (out[0] != '/') out = std::string(cwd) + "/" + out;
     RTCDevice dev = rtcNewDevice(nullptr);
     parallel_init(1);
     Scene scene = parse_scene(scene_file, dev);
+    if (res_w > 0) { scene.camera.width = res_w; scene.camera.height = res_h; }
     int w = scene.camera.width, h = scene.camera.height;
-    struct Rec { float t, u, v; int geom, prim; };
-    std::vector<Rec> recs(w * h);
+    SeamRec blank; memset(&blank, 0, sizeof blank); blank.geom = blank.prim = -1;
+    std::vector<SeamRec> prim(w * h, blank), bounce(w * h, blank), shadow(w * h, blank);
+    const Real eps = get_shadow_epsilon(scene);
+    long n_hit = 0, n_bhit = 0, n_occl = 0, n_sh = 0;
     for (int y = 0; y < h; y++) for (int x = 0; x < w; x++) {
+        int i = y * w + x;
         Ray ray = sample_primary(scene.camera, Vector2((x + Real(0.5)) / w, (y + Real(0.5)) / h));
-        Rec r{0, 0, 0, -1, -1};
-        if (std::optional<PathVertex> v = intersect(scene, ray, init_ray_differential(w, h))) {
-            r.t = (float)distance(v->position, ray.org); r.u = (float)v->st[0]; r.v = (float)v->st[1];
-            r.geom = v->shape_id; r.prim = v->primitive_id;
+        seam_set_ray(prim[i], ray);
+        std::optional<PathVertex> v = intersect(scene, ray, init_ray_differential(w, h));
+        seam_set_hit(prim[i], ray, v);
+        if (!v) continue;
+        n_hit++;
+        pcg32_state rng = init_pcg32((uint64_t)i);
+        // bounce: uniform direction on the sphere, flipped into the hemisphere of the geometric normal
+        Real z = 1 - 2 * next_pcg32_real<Real>(rng), phi = 2 * c_PI * next_pcg32_real<Real>(rng);
+        Real rr = sqrt(max(Real(0), 1 - z * z));
+        Vector3 d{rr * cos(phi), rr * sin(phi), z};
+        if (dot(d, v->geometry_normal) < 0) d = -d;
+        Ray bray{v->position, d, get_intersection_epsilon(scene), infinity<Real>()};
+        seam_set_ray(bounce[i], bray);
+        std::optional<PathVertex> bv = intersect(scene, bray);
+        seam_set_hit(bounce[i], bray, bv);
+        if (bv) n_bhit++;
+        // shadow: path_tracing.h:97-127
+        if (scene.lights.empty()) continue;
+        Vector2 light_uv{next_pcg32_real<Real>(rng), next_pcg32_real<Real>(rng)};
+        Real light_w = next_pcg32_real<Real>(rng);
+        Real shape_w = next_pcg32_real<Real>(rng);
+        int light_id = sample_light(scene, light_w);
+        const Light &light = scene.lights[light_id];
+        PointAndNormal pl = sample_point_on_light(light, v->position, light_uv, shape_w, scene);
+        Ray sray;
+        if (!is_envmap(light)) {
+            Vector3 dir_light = normalize(pl.position - v->position);
+            sray = Ray{v->position, dir_light, eps, (1 - eps) * distance(pl.position, v->position)};
+        } else {
+            sray = Ray{v->position, -pl.normal, eps, infinity<Real>()};
         }
-        recs[y * w + x] = r;
+        seam_set_ray(shadow[i], sray);
+        shadow[i].occl = occluded(scene, sray) ? 1 : 0;
+        n_sh++; n_occl += shadow[i].occl;
     }
     std::ofstream f(out, std::ios::binary);
-    f.write((const char *)&w, 4); f.write((const char *)&h, 4);
-    f.write((const char *)recs.data(), recs.size() * sizeof(Rec));
-    printf("wrote %d x %d hit records to %s\n", w, h, out.c_str());
+    int hdr[4] = {w, h, 3, 3};
+    f.write((const char *)hdr, sizeof hdr);
+    f.write((const char *)prim.data(), prim.size() * sizeof(SeamRec));
+    f.write((const char *)bounce.data(), bounce.size() * sizeof(SeamRec));
+    f.write((const char *)shadow.data(), shadow.size() * sizeof(SeamRec));
+    printf("seam %d x %d: %ld primary hits, %ld bounce hits, %ld of %ld shadow rays occluded -> %s\n", w, h, n_hit, n_bhit, n_occl, n_sh, out.c_str());
     parallel_cleanup();
+    if (g_seam_mismatch) { fprintf(stderr, "seam dump: %ld records disagree with the PathVertex of intersect()\n", g_seam_mismatch); return 3; }
     return 0;
 }
 
