@@ -169,7 +169,17 @@ typedef struct lj_render_params {
     int32_t max_depth_override;    /* -100 => scene options */
     int32_t paths_in_flight;       /* wavefront pool size, 0 => auto */
     int32_t flags;                 /* bit0: count traversal steps (nodes / prims per ray); bit1: per-stage CUDA-event times */
+    int32_t partition;             /* LJ_PARTITION_*: how a multi-device context (lj_init_devices) splits one render */
 } lj_render_params;
+
+/* Work split of ONE render over the devices of a multi-device context; the scene is replicated, every
+ * device renders its share into its own f64 sums, and the sums are added with one NCCL reduce to the first device.
+ *   TILES  the 16x16 tiles of render.cpp:75-82 dealt round-robin (tile id % n_devices): disjoint pixels, so the reduced
+ *          image is bit-identical to the one-device image for every device count and every integrator / RNG mode;
+ *   SPP    device i renders a contiguous slice of the samples of EVERY pixel (balanced when cost is spatially skewed);
+ *          needs per-sample streams (LJ_RNG_SAMPLE_STREAMS) and a sampling integrator, otherwise TILES is used.
+ * AUTO = TILES.  Ignored by one-device contexts and when the caller sets tile_world / a sample slice itself. */
+enum { LJ_PARTITION_AUTO = 0, LJ_PARTITION_TILES = 1, LJ_PARTITION_SPP = 2 };
 
 typedef struct lj_stats {
     double render_ms;              /* CUDA-event time of the whole render on the device */
@@ -183,6 +193,10 @@ typedef struct lj_stats {
     uint64_t shadow_nodes_visited, shadow_prims_tested;   /* flags bit0, any-hit rays */
     uint64_t iterations;                  /* wavefront iterations */
     double tables_build_ms;               /* lj_scene_create_ex with LJ_SCENE_BUILD_TABLES: device time of the scene build step */
+    /* multi-device contexts: render_ms = slowest device's render + the reduce; the counters above are sums over devices */
+    int32_t n_devices, partition;         /* devices that rendered; LJ_PARTITION_* actually used */
+    double reduce_ms;                     /* NCCL reduce of the f64 sums, CUDA-event time on the root device */
+    double device_ms_min, device_ms_max;  /* fastest / slowest device's render (CUDA events on each device) */
 } lj_stats;
 
 typedef struct lj_ray { float org[3], tnear, dir[3], tfar; } lj_ray;           /* RTCRay subset, f32 seam */
@@ -193,6 +207,15 @@ typedef struct lj_scene lj_scene;
 
 /* ---- entry points ---- */
 int lj_init(int device_id, lj_ctx **out);                      /* replaces rtcNewDevice + parallel_init (main.cpp:30-31) */
+/* The same for several devices of one box: replaces parallel_init(num_threads) + the tile
+ * parallel_for of render.cpp:75-98 as the unit that fans one render out.  device_ids NULL / n_devices <= 0 = every
+ * visible device.  lj_scene_create on such a context uploads the scene and builds the BVH on every device (one host
+ * thread per device); lj_render / lj_render_device split the work (lj_render_params.partition), and add the per-device
+ * sums with ncclReduce (NCCL is loaded with dlopen("libnccl.so.2") the first time it is needed; without it a
+ * multi-device render fails with LJ_EUNSUPPORTED -- there is no host-side fallback for the reduction).  Every other
+ * entry point that takes the context or one of its scenes uses the first device. */
+int lj_init_devices(const int *device_ids, int n_devices, lj_ctx **out);
+int lj_ctx_device_count(lj_ctx *ctx);                          /* devices behind a context (1 for lj_init) */
 void lj_shutdown(lj_ctx *ctx);                                 /* main.cpp:47-48 */
 int lj_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, lj_scene **out);   /* Scene::Scene's Embree build, scene.cpp:20-34 */
 /* Scene build step on the device (scene.cpp:36-52 minus the Embree build).  With

@@ -17,8 +17,15 @@ void lj_set_error(const char *fmt, ...) {
     va_end(ap);
 }
 extern "C" const char *lj_last_error(void) { return g_err; }
+const char *lj_error_text() { return g_err; }
 
-extern "C" int lj_init(int device_id, lj_ctx **out) {
+extern "C" int lj_init(int device_id, lj_ctx **out) { return lj_init_single(device_id, out); }
+extern "C" void lj_shutdown(lj_ctx *ctx) {
+    if (!ctx) return;
+    if (ctx->group) lj_group_shutdown(ctx); else lj_shutdown_single(ctx);
+}
+
+int lj_init_single(int device_id, lj_ctx **out) {
     if (!out) { lj_set_error("lj_init: out is null"); return LJ_EINVAL; }
     int n = 0;
     cudaError_t e = cudaGetDeviceCount(&n);
@@ -29,7 +36,7 @@ extern "C" int lj_init(int device_id, lj_ctx **out) {
     if (device_id < 0 || device_id >= n) { lj_set_error("lj_init: device %d out of range [0,%d)", device_id, n); return LJ_EINVAL; }
     LJ_CUDA(cudaSetDevice(device_id));
     lj_ctx *c = new lj_ctx();
-    c->device = device_id; c->wf_pool = nullptr; c->wf_pool_bytes = 0;
+    c->device = device_id; c->wf_pool = nullptr; c->wf_pool_bytes = 0; c->group = nullptr;
     {   // keep freed blocks in the device's default memory pool (see lj_alloc.h)
         cudaMemPool_t pool;
         LJ_CUDA(cudaDeviceGetDefaultMemPool(&pool, device_id));
@@ -40,7 +47,7 @@ extern "C" int lj_init(int device_id, lj_ctx **out) {
     *out = c;
     return LJ_OK;
 }
-extern "C" void lj_shutdown(lj_ctx *ctx) {
+void lj_shutdown_single(lj_ctx *ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     if (ctx->wf_pool) lj_free(ctx->wf_pool);
@@ -86,24 +93,95 @@ struct Uploader {
     }
 };
 
+// Every id, kind and offset of a description is range-checked here, once, on the host: the kernels index with them
+// unchecked, and descriptions also come from .ljs files (lj_scene_desc_load).
 static int validate_desc(const lj_scene_desc *d) {
-    if (d->camera.width <= 0 || d->camera.height <= 0) { lj_set_error("scene: bad resolution %dx%d", d->camera.width, d->camera.height); return LJ_EINVAL; }
+#define BAD(...) do { lj_set_error(__VA_ARGS__); return LJ_EINVAL; } while (0)
+    typedef unsigned long long ull;
+    if (d->camera.width <= 0 || d->camera.height <= 0) BAD("scene: bad resolution %dx%d", d->camera.width, d->camera.height);
+    if ((long long)d->camera.width * d->camera.height > (1LL << 28)) BAD("scene: film of %dx%d pixels is too large", d->camera.width, d->camera.height);
+    if (d->camera.filter_kind < LJ_FILTER_BOX || d->camera.filter_kind > LJ_FILTER_GAUSSIAN) BAD("scene: unknown pixel filter %d", d->camera.filter_kind);
+    if (d->camera.medium_id < -1 || d->camera.medium_id >= (long long)d->num_media) BAD("scene: camera medium id out of range");
+    if (d->options.integrator < LJ_INTEGRATOR_DEPTH || d->options.integrator > LJ_INTEGRATOR_VOLPATH) BAD("scene: unknown integrator %d", d->options.integrator);
+    if (d->envmap_light_id < -1 || d->envmap_light_id >= (long long)d->num_lights) BAD("scene: envmap light id out of range");
+    if (d->num_shapes > 0x7fffffffu || d->num_lights > 0x7fffffffu || d->num_materials > 0x7fffffffu || d->num_media > 0x7fffffffu ||
+        d->num_textures > 0x7fffffffu || d->num_images1 > 0x7fffffffu || d->num_images3 > 0x7fffffffu || d->num_indices > 0x7fffffffu / 3 ||
+        d->num_positions > 0x7fffffffu) BAD("scene: record count out of range");
+    auto in_tables = [&](uint64_t off, uint64_t n) { return off <= d->num_tables && n <= d->num_tables - off; };
+    for (uint64_t i = 0; i < d->num_images1 + d->num_images3; i++) {
+        const bool one = i < d->num_images1;
+        const lj_image &im = one ? d->images1[i] : d->images3[i - d->num_images1];
+        if (im.channels != (one ? 1 : 3) || im.num_levels < 1 || im.num_levels > 8) BAD("scene: image %llu has bad channels / level count", (ull)i);
+        for (int l = 0; l < im.num_levels; l++) {
+            if (im.width[l] <= 0 || im.height[l] <= 0) BAD("scene: image %llu level %d is empty", (ull)i, l);
+            const uint64_t n = (uint64_t)im.width[l] * (uint64_t)im.height[l] * (uint64_t)im.channels;
+            if (im.offset[l] > d->num_texels || n > d->num_texels - im.offset[l]) BAD("scene: image %llu level %d lies outside the texel array", (ull)i, l);
+        }
+    }
+    for (uint64_t i = 0; i < d->num_textures; i++) {
+        const lj_texture &t = d->textures[i];
+        if (t.kind < LJ_TEX_CONSTANT || t.kind > LJ_TEX_CHECKERBOARD || (t.channels != 1 && t.channels != 3)) BAD("scene: texture %llu has an unknown kind / channel count", (ull)i);
+        if (t.kind == LJ_TEX_IMAGE && (t.image_id < 0 || (uint64_t)t.image_id >= (t.channels == 1 ? d->num_images1 : d->num_images3)))
+            BAD("scene: texture %llu image id out of range", (ull)i);
+    }
+    for (uint64_t i = 0; i < d->num_materials; i++) {
+        const lj_material &m = d->materials[i];
+        if (m.kind < 0 || m.kind >= LJ_MAT_KIND_COUNT) BAD("scene: material %llu has unknown kind %d", (ull)i, m.kind);
+        for (int k = 0; k < LJ_SLOT_COUNT; k++)
+            if (m.tex[k] < -1 || m.tex[k] >= (long long)d->num_textures) BAD("scene: material %llu texture slot %d out of range", (ull)i, k);
+    }
+    for (uint64_t i = 0; i < d->num_media; i++) {
+        const lj_medium &m = d->media[i];
+        if (m.kind < LJ_MEDIUM_HOMOGENEOUS || m.kind > LJ_MEDIUM_HETEROGENEOUS || m.phase_kind < LJ_PHASE_ISOTROPIC || m.phase_kind > LJ_PHASE_HG)
+            BAD("scene: medium %llu has an unknown kind / phase function", (ull)i);
+        const lj_volume *vols[2] = {&m.albedo, &m.density};
+        for (const lj_volume *v : vols) {
+            if (m.kind != LJ_MEDIUM_HETEROGENEOUS) continue;
+            if (v->kind < LJ_VOLUME_CONSTANT || v->kind > LJ_VOLUME_GRID) BAD("scene: medium %llu has an unknown volume kind", (ull)i);
+            if (v->kind != LJ_VOLUME_GRID) continue;
+            if (v->resolution[0] <= 0 || v->resolution[1] <= 0 || v->resolution[2] <= 0) BAD("scene: medium %llu has an empty grid", (ull)i);
+            const uint64_t n = 3ull * (uint64_t)v->resolution[0] * (uint64_t)v->resolution[1] * (uint64_t)v->resolution[2];
+            if (v->resolution[0] > 4096 || v->resolution[1] > 4096 || v->resolution[2] > 4096 || v->data_offset > d->num_grid_data || n > d->num_grid_data - v->data_offset)
+                BAD("scene: medium %llu grid lies outside the grid array", (ull)i);
+        }
+    }
     for (uint64_t i = 0; i < d->num_shapes; i++) {
         const lj_shape &s = d->shapes[i];
+        if (s.kind != LJ_SHAPE_SPHERE && s.kind != LJ_SHAPE_MESH) BAD("scene: shape %llu has unknown kind %d", (ull)i, s.kind);
+        if (s.material_id < -1 || s.material_id >= (long long)d->num_materials) BAD("scene: shape %llu material id out of range", (ull)i);
+        if (s.area_light_id < -1 || s.area_light_id >= (long long)d->num_lights) BAD("scene: shape %llu area light id out of range", (ull)i);
+        if (s.interior_medium_id < -1 || s.interior_medium_id >= (long long)d->num_media || s.exterior_medium_id < -1 || s.exterior_medium_id >= (long long)d->num_media)
+            BAD("scene: shape %llu medium id out of range", (ull)i);
+        if (s.material_id < 0 && d->options.integrator == LJ_INTEGRATOR_PATH) BAD("scene: shape %llu has no material (index-matched surfaces need the volpath integrator)", (ull)i);
         if (s.kind == LJ_SHAPE_MESH) {
-            if ((uint64_t)s.vertex_offset + s.num_vertices > d->num_positions || (uint64_t)s.triangle_offset + s.num_triangles > d->num_indices) {
-                lj_set_error("scene: shape %llu mesh ranges out of bounds", (unsigned long long)i); return LJ_EINVAL;
-            }
-            for (uint32_t t = 0; t < s.num_triangles * 3; t++) {
+            if ((uint64_t)s.vertex_offset + s.num_vertices > d->num_positions || (uint64_t)s.triangle_offset + s.num_triangles > d->num_indices)
+                BAD("scene: shape %llu mesh ranges out of bounds", (ull)i);
+            for (uint64_t t = 0; t < (uint64_t)s.num_triangles * 3; t++) {
                 int idx = d->indices[3 * (size_t)s.triangle_offset + t];
-                if (idx < 0 || (uint32_t)idx >= s.num_vertices) { lj_set_error("scene: shape %llu has an out-of-range vertex index", (unsigned long long)i); return LJ_EINVAL; }
+                if (idx < 0 || (uint32_t)idx >= s.num_vertices) BAD("scene: shape %llu has an out-of-range vertex index", (ull)i);
             }
+            if (s.area_light_id >= 0 && (!in_tables(s.tri_cdf_offset, (uint64_t)s.num_triangles + 1) || !in_tables(s.tri_pmf_offset, s.num_triangles)))
+                BAD("scene: shape %llu sampling tables lie outside the table array", (ull)i);
         }
-        if (s.material_id >= (int)d->num_materials) { lj_set_error("scene: shape %llu material id out of range", (unsigned long long)i); return LJ_EINVAL; }
     }
-    if ((d->options.integrator == LJ_INTEGRATOR_PATH || d->options.integrator == LJ_INTEGRATOR_VOLPATH) && d->num_lights == 0) {
-        lj_set_error("scene: no lights (the reference asserts in sample(TableDist1D), table_dist.cpp:29)"); return LJ_EINVAL;
+    for (uint64_t i = 0; i < d->num_lights; i++) {
+        const lj_light &l = d->lights[i];
+        if (l.kind == LJ_LIGHT_AREA) {
+            if (l.shape_id < 0 || (uint64_t)l.shape_id >= d->num_shapes) BAD("scene: light %llu shape id out of range", (ull)i);
+        } else if (l.kind == LJ_LIGHT_ENVMAP) {
+            if (l.values_texture < 0 || (uint64_t)l.values_texture >= d->num_textures) BAD("scene: envmap %llu texture id out of range", (ull)i);
+            if (l.dist_width <= 0 || l.dist_height <= 0) BAD("scene: envmap %llu has an empty sampling table", (ull)i);
+            const uint64_t w = (uint64_t)l.dist_width, h = (uint64_t)l.dist_height;
+            if (!in_tables(l.cdf_rows_offset, h * (w + 1)) || !in_tables(l.pdf_rows_offset, h * w) ||
+                !in_tables(l.cdf_marginals_offset, h + 1) || !in_tables(l.pdf_marginals_offset, h))
+                BAD("scene: envmap %llu sampling tables lie outside the table array", (ull)i);
+        } else BAD("scene: light %llu has unknown kind %d", (ull)i, l.kind);
     }
+    if (d->num_lights && (!in_tables(d->light_pmf_offset, d->num_lights) || !in_tables(d->light_cdf_offset, d->num_lights + 1)))
+        BAD("scene: light distribution lies outside the table array");
+    if ((d->options.integrator == LJ_INTEGRATOR_PATH || d->options.integrator == LJ_INTEGRATOR_VOLPATH) && d->num_lights == 0)
+        BAD("scene: no lights (the reference asserts in sample(TableDist1D), table_dist.cpp:29)");
+#undef BAD
     return LJ_OK;
 }
 
@@ -117,11 +195,20 @@ extern "C" int lj_scene_create_ex(lj_ctx *ctx, const lj_scene_desc *desc, uint32
     if (!ctx || !desc || !out) { lj_set_error("lj_scene_create: null argument"); return LJ_EINVAL; }
     int rc = validate_desc(desc);
     if (rc) return rc;
+    return ctx->group ? lj_group_scene_create(ctx, desc, flags, out) : lj_scene_create_single(ctx, desc, flags, out);
+}
+
+// `desc` has been validated
+int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flags, lj_scene **out) {
+    int rc;
     LJ_CUDA(cudaSetDevice(ctx->device));
     lj_scene *s = new lj_scene();
     s->ctx = ctx;
     memset(&s->build_stats, 0, sizeof s->build_stats);
     memset(&s->bvh, 0, sizeof s->bvh);
+    memset(s->kind_present, 0, sizeof s->kind_present); s->grid_media = false;
+    for (uint64_t i = 0; i < desc->num_materials; i++) s->kind_present[desc->materials[i].kind] = true;   // kinds validated above
+    for (uint64_t i = 0; i < desc->num_media; i++) s->grid_media = s->grid_media || desc->media[i].kind == LJ_MEDIUM_HETEROGENEOUS;
     DScene &d = s->d;
     memset(&d, 0, sizeof d);
     cudaEvent_t e0, e1, e2;
@@ -156,13 +243,15 @@ extern "C" int lj_scene_create_ex(lj_ctx *ctx, const lj_scene_desc *desc, uint32
     const int *d_tri_shape; const SpherePrim *d_spheres;
     up.add(tri_shape.data(), tri_shape.size(), &d_tri_shape);
     up.add(spheres.data(), spheres.size(), &d_spheres);
-    if ((rc = up.commit(s)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+    if ((rc = up.commit(s)) != LJ_OK) { cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc; }
     d.light_pmf = d.tables + desc->light_pmf_offset;
     d.light_cdf = d.tables + desc->light_cdf_offset;
     cudaEventRecord(e1);
     if (flags & LJ_SCENE_BUILD_TABLES) {
         float tms = 0;
-        if ((rc = lj_scene_build_tables(s, desc, (flags & LJ_SCENE_POISON_DERIVED) != 0, &tms)) != LJ_OK) { lj_scene_destroy(s); return rc; }
+        if ((rc = lj_scene_build_tables(s, desc, (flags & LJ_SCENE_POISON_DERIVED) != 0, &tms)) != LJ_OK) {
+            cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc;
+        }
         s->build_stats.tables_build_ms = tms;
         cudaEventRecord(e1);
     }
@@ -171,7 +260,10 @@ extern "C" int lj_scene_create_ex(lj_ctx *ctx, const lj_scene_desc *desc, uint32
     bi.num_tris = (int)desc->num_indices; bi.num_spheres = (int)spheres.size();
     bi.positions = d.positions; bi.indices = d.indices; bi.tri_shape = d_tri_shape; bi.shapes = d.shapes; bi.spheres = d_spheres;
     char berr[256] = "";
-    if (lj_bvh_build(bi, s->bvh, berr) != 0) { lj_set_error("BVH build failed: %s", berr); lj_scene_destroy(s); return LJ_ECUDA; }
+    if (lj_bvh_build(bi, s->bvh, berr) != 0) {
+        lj_set_error("BVH build failed: %s", berr);
+        cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return LJ_ECUDA;
+    }
     cudaEventRecord(e2);
     cudaEventSynchronize(e2);
     d.num_tris = bi.num_tris; d.num_spheres = bi.num_spheres; d.num_prims = s->bvh.num_prims;
@@ -194,6 +286,11 @@ extern "C" int lj_scene_create_ex(lj_ctx *ctx, const lj_scene_desc *desc, uint32
 
 extern "C" void lj_scene_destroy(lj_scene *s) {
     if (!s) return;
+    if (!s->replicas.empty()) lj_group_scene_destroy(s); else lj_scene_destroy_single(s);
+}
+void lj_scene_destroy_single(lj_scene *s) {
+    if (!s) return;
+    cudaSetDevice(s->ctx->device);
     for (void *p : s->allocs) lj_free(p);
     lj_bvh_free(s->bvh);
     delete s;
@@ -202,6 +299,7 @@ extern "C" void lj_scene_destroy(lj_scene *s) {
 extern "C" int lj_scene_read_derived(lj_scene *s, double *tables, uint64_t num_tables, double *texels, uint64_t num_texels,
                                      lj_shape *shapes, uint64_t num_shapes, lj_light *lights, uint64_t num_lights) {
     if (!s) { lj_set_error("lj_scene_read_derived: null scene"); return LJ_EINVAL; }
+    if (!s->replicas.empty()) s = s->replicas[0];
     LJ_CUDA(cudaSetDevice(s->ctx->device));
     if (tables && num_tables) LJ_CUDA(cudaMemcpy(tables, s->d.tables, sizeof(double) * num_tables, cudaMemcpyDeviceToHost));
     if (texels && num_texels) LJ_CUDA(cudaMemcpy(texels, s->d.texels, sizeof(double) * num_texels, cudaMemcpyDeviceToHost));
@@ -212,10 +310,13 @@ extern "C" int lj_scene_read_derived(lj_scene *s, double *tables, uint64_t num_t
 
 extern "C" int lj_scene_info(lj_scene *s, int32_t *width, int32_t *height, int32_t *spp, lj_stats *build_stats) {
     if (!s) { lj_set_error("lj_scene_info: null scene"); return LJ_EINVAL; }
+    const lj_stats handle_stats = s->build_stats;
+    const bool multi = !s->replicas.empty();
+    if (multi) s = s->replicas[0];
     if (width) *width = s->d.camera.width;
     if (height) *height = s->d.camera.height;
     if (spp) *spp = s->d.options.samples_per_pixel;
-    if (build_stats) *build_stats = s->build_stats;
+    if (build_stats) *build_stats = multi ? handle_stats : s->build_stats;
     return LJ_OK;
 }
 
@@ -235,6 +336,13 @@ static int make_launch(lj_scene *s, const lj_render_params *params, RenderLaunch
     rl.s_begin = 0; rl.s_end = rl.spp;
     if (p.sample_end > p.sample_begin) { rl.s_begin = p.sample_begin; rl.s_end = p.sample_end; }
     if (rl.spp <= 0) { lj_set_error("render: spp must be positive"); return LJ_EINVAL; }
+    if (rl.s_begin < 0 || rl.s_end > rl.spp) { lj_set_error("render: sample slice [%d,%d) outside [0,%d)", rl.s_begin, rl.s_end, rl.spp); return LJ_EINVAL; }
+    const int integ = s->d.options.integrator;
+    const bool sampling = integ == LJ_INTEGRATOR_PATH || integ == LJ_INTEGRATOR_VOLPATH;
+    // the tile-serial engine consumes ONE stream per tile over all samples (render.cpp:82-96): a slice of it does not exist
+    if ((rl.s_begin != 0 || rl.s_end != rl.spp) && (p.rng_mode == LJ_RNG_TILE_STREAMS || !sampling)) {
+        lj_set_error("render: a sample slice needs per-sample streams (LJ_RNG_SAMPLE_STREAMS) and a sampling integrator"); return LJ_EINVAL;
+    }
     if (p.tile_world < 0 || (p.tile_world > 0 && (p.tile_rank < 0 || p.tile_rank >= p.tile_world))) { lj_set_error("render: bad tile partition %d/%d", p.tile_rank, p.tile_world); return LJ_EINVAL; }
     rl.width = s->d.camera.width; rl.height = s->d.camera.height;
     rl.ntx = (rl.width + 15) / 16; rl.nty = (rl.height + 15) / 16;
@@ -243,6 +351,10 @@ static int make_launch(lj_scene *s, const lj_render_params *params, RenderLaunch
 
 extern "C" int lj_render_device(lj_scene *s, const lj_render_params *params, double *dev_sum, lj_stats *stats) {
     if (!s || !dev_sum) { lj_set_error("lj_render_device: null argument"); return LJ_EINVAL; }
+    return s->replicas.empty() ? lj_render_device_single(s, params, dev_sum, stats) : lj_group_render_device(s, params, dev_sum, stats);
+}
+
+int lj_render_device_single(lj_scene *s, const lj_render_params *params, double *dev_sum, lj_stats *stats) {
     LJ_CUDA(cudaSetDevice(s->ctx->device));
     RenderLaunch rl;
     int rc = make_launch(s, params, rl);
@@ -271,22 +383,29 @@ extern "C" int lj_render_device(lj_scene *s, const lj_render_params *params, dou
     float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
     st.render_ms = ms;
+    st.n_devices = 1; st.partition = LJ_PARTITION_AUTO; st.reduce_ms = 0; st.device_ms_min = st.device_ms_max = ms;
     if (stats) *stats = st;
     return rc;
 }
 
 extern "C" int lj_render(lj_scene *s, const lj_render_params *params, float *rgb_out, lj_stats *stats) {
     if (!s || !rgb_out) { lj_set_error("lj_render: null argument"); return LJ_EINVAL; }
-    LJ_CUDA(cudaSetDevice(s->ctx->device));
-    int npix = s->d.camera.width * s->d.camera.height;
+    lj_scene *s0 = s->replicas.empty() ? s : s->replicas[0];
+    LJ_CUDA(cudaSetDevice(s0->ctx->device));
+    const int npix = s0->d.camera.width * s0->d.camera.height;
+    RenderLaunch rl;
+    int rc = make_launch(s0, params, rl);
+    if (rc) return rc;
     double *sum = nullptr; float *rgb = nullptr;
     LJ_CUDA(lj_malloc(&sum, sizeof(double) * 3 * (size_t)npix));
-    LJ_CUDA(lj_malloc(&rgb, sizeof(float) * 3 * (size_t)npix));
-    int rc = lj_render_device(s, params, sum, stats);
+    if (lj_malloc(&rgb, sizeof(float) * 3 * (size_t)npix) != cudaSuccess) { lj_free(sum); lj_set_error("lj_render: out of device memory"); return LJ_ECUDA; }
+    // the buffers are allocated in this thread's stream; a multi-device render writes them from its worker threads
+    if (!s->replicas.empty()) cudaStreamSynchronize(0);
+    rc = lj_render_device(s, params, sum, stats);
     if (rc == LJ_OK) {
-        RenderLaunch rl; make_launch(s, params, rl);
-        int integ = s->d.options.integrator;
-        double denom = (integ == LJ_INTEGRATOR_PATH || integ == LJ_INTEGRATOR_VOLPATH) ? (double)(rl.s_end - rl.s_begin) : 1.0;
+        cudaSetDevice(s0->ctx->device);
+        const int integ = s0->d.options.integrator;
+        const double denom = (integ == LJ_INTEGRATOR_PATH || integ == LJ_INTEGRATOR_VOLPATH) ? (double)(rl.s_end - rl.s_begin) : 1.0;
         k_finalize<<<(npix * 3 + 255) / 256, 256>>>(npix, sum, 1.0 / denom, rgb);
         cudaError_t e = cudaMemcpy(rgb_out, rgb, sizeof(float) * 3 * (size_t)npix, cudaMemcpyDeviceToHost);
         if (e != cudaSuccess) { lj_set_error("lj_render: D2H failed: %s", cudaGetErrorString(e)); rc = LJ_ECUDA; }
@@ -318,13 +437,16 @@ __global__ void k_intersect_batch(DScene sc, const lj_ray *rays, long long n, lj
 extern "C" int lj_intersect_batch(lj_scene *s, const lj_ray *rays, int64_t n, lj_hit *hits, int any_hit) {
     if (!s || (n > 0 && (!rays || !hits))) { lj_set_error("lj_intersect_batch: null argument"); return LJ_EINVAL; }
     if (n <= 0) return LJ_OK;
+    if (!s->replicas.empty()) s = s->replicas[0];
     LJ_CUDA(cudaSetDevice(s->ctx->device));
     lj_ray *dr = nullptr; lj_hit *dh = nullptr;
     LJ_CUDA(lj_malloc(&dr, sizeof(lj_ray) * n));
-    LJ_CUDA(lj_malloc(&dh, sizeof(lj_hit) * n));
-    cudaMemcpy(dr, rays, sizeof(lj_ray) * n, cudaMemcpyHostToDevice);
-    k_intersect_batch<<<(unsigned)((n + 127) / 128), 128>>>(s->d, dr, n, dh, any_hit);
-    cudaError_t e = cudaMemcpy(hits, dh, sizeof(lj_hit) * n, cudaMemcpyDeviceToHost);
+    cudaError_t e = lj_malloc(&dh, sizeof(lj_hit) * n);
+    if (e == cudaSuccess) e = cudaMemcpy(dr, rays, sizeof(lj_ray) * n, cudaMemcpyHostToDevice);
+    if (e == cudaSuccess) {
+        k_intersect_batch<<<(unsigned)((n + 127) / 128), 128>>>(s->d, dr, n, dh, any_hit);
+        e = cudaMemcpy(hits, dh, sizeof(lj_hit) * n, cudaMemcpyDeviceToHost);
+    }
     lj_free(dr); lj_free(dh);
     if (e != cudaSuccess) { lj_set_error("lj_intersect_batch: %s", cudaGetErrorString(e)); return LJ_ECUDA; }
     return LJ_OK;

@@ -56,6 +56,11 @@ extern "C" int lj_scene_desc_load(const char *path, lj_scene_desc **out) {
     void *bufs[NARR] = {0};
     bool ok = fread(magic, 1, 4, f) == 4 && memcmp(magic, "LJS1", 4) == 0 && fread(d, sizeof *d, 1, f) == 1;
     Arr expect[NARR];
+    if (ok) {   // counts come from the file: keep count * record size far from wrapping around 2^64
+        const uint64_t counts[] = {d->num_shapes, d->num_lights, d->num_materials, d->num_media, d->num_textures, d->num_images1,
+                                   d->num_images3, d->num_positions, d->num_indices, d->num_texels, d->num_tables, d->num_grid_data};
+        for (uint64_t c : counts) ok = ok && c < (1ull << 40);
+    }
     if (ok) arrays_of(d, expect);
     for (int i = 0; ok && i < NARR; i++) {
         uint64_t bytes = 0;

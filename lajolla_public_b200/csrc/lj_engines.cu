@@ -146,11 +146,15 @@ int lj_render_volpath(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
 }
 
 // ---------------- primary-ray AOV integrators (render.cpp:12-69) ----------------
-__global__ void k_aux(DScene sc, double *sum) {
+__global__ void k_aux(DScene sc, int ntx, int tile_rank, int tile_world, double *sum) {
     int pix = blockIdx.x * blockDim.x + threadIdx.x;
     int w = sc.camera.width, h = sc.camera.height;
     if (pix >= w * h) return;
     int x = pix % w, y = pix / w;
+    if (tile_world > 0 && (((y / 16) * ntx + (x / 16)) % tile_world) != tile_rank) {     // another rank's tile
+        sum[3 * (size_t)pix] = 0; sum[3 * (size_t)pix + 1] = 0; sum[3 * (size_t)pix + 2] = 0;
+        return;
+    }
     Ray ray = sample_primary(sc.camera, mk2((x + 0.5) / w, (y + 0.5) / h));
     RayDiff rd = init_ray_differential(w, h);
     d3 color = mk3(0.0);
@@ -179,7 +183,7 @@ __global__ void k_aux(DScene sc, double *sum) {
 
 int lj_render_aux(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st) {
     int npix = rl.width * rl.height;
-    k_aux<<<(npix + 127) / 128, 128>>>(s->d, dev_sum);
+    k_aux<<<(npix + 127) / 128, 128>>>(s->d, rl.ntx, rl.p.tile_rank, rl.p.tile_world, dev_sum);
     LJ_CUDA(cudaGetLastError());
     st->kernel_launches += 1; st->samples = npix; st->rays_primary = npix;
     return LJ_OK;

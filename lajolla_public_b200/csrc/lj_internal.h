@@ -7,12 +7,16 @@
 
 void lj_set_error(const char *fmt, ...);
 
+struct LjDeviceGroup;
 struct lj_ctx {
     int device;
     int sm_count;
     // wavefront path-slot arena: grown on demand, shared by every scene of the context (renders are
     // synchronous and the ABI is single-threaded per context), freed by lj_shutdown
     void *wf_pool; size_t wf_pool_bytes;
+    // multi-device contexts (lj_init_devices, lj_multi.cu): the per-device contexts, worker threads and NCCL
+    // communicators; null for a one-device context.  `this` is then only the handle and mirrors device 0.
+    LjDeviceGroup *group;
 };
 int lj_ctx_arena(lj_ctx *ctx, size_t bytes, void **out);
 
@@ -22,7 +26,23 @@ struct lj_scene {
     std::vector<void *> allocs;     // every cudaMalloc owned by the scene
     BvhBuildOutput bvh;
     lj_stats build_stats;
+    bool kind_present[LJ_MAT_KIND_COUNT];   // material kinds the scene uses (one shade launch per kind)
+    bool grid_media;                        // any heterogeneous medium (the tracking kernels run)
+    std::vector<lj_scene *> replicas;       // multi-device contexts: one scene per device (this object is only the handle)
 };
+
+// one-device implementations behind the C ABI (lj_api.cu); the multi-device layer (lj_multi.cu) calls them per device
+int lj_init_single(int device_id, lj_ctx **out);
+void lj_shutdown_single(lj_ctx *ctx);
+int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flags, lj_scene **out);
+void lj_scene_destroy_single(lj_scene *s);
+int lj_render_device_single(lj_scene *s, const lj_render_params *params, double *dev_sum, lj_stats *stats);
+// multi-device layer
+void lj_group_shutdown(lj_ctx *ctx);
+int lj_group_scene_create(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flags, lj_scene **out);
+void lj_group_scene_destroy(lj_scene *s);
+int lj_group_render_device(lj_scene *s, const lj_render_params *params, double *dev_sum, lj_stats *stats);
+const char *lj_error_text();
 
 struct RenderLaunch {
     lj_render_params p;

@@ -71,8 +71,8 @@ struct __align__(16) VolTrack {
 };                                          // 144 B
 
 struct VolPool {
-    int capacity, K;
-    long long npix;
+    int capacity;               // = map.K * map.npix_local slots
+    SlotMap map;                // slot -> pixel / sample lane / accumulator (lj_wave_common.cuh)
     VolPath *path; VolNee *nee; HitRec *hit, *nee_hit; VolTrack *track;
     double *accum;
     ExtRec *ext_ray; int *ext_slot;
@@ -81,10 +81,10 @@ struct VolPool {
     int *counts;
 };
 
-LJ_D void vol_terminate(const VolPool &vp, int slot, d3 L) {
+LJ_D void vol_terminate(const VolPool &vp, int slot, int sample, d3 L) {
     // render.cpp:140 with vector.h:289-292: a sample is dropped only if ALL channels are non-finite
     if (isfinite(L.x) || isfinite(L.y) || isfinite(L.z)) {
-        double *a = vp.accum + 3 * (size_t)slot;
+        double *a = vp.accum + accum_offset(vp.map, slot, sample);
         a[0] += L.x; a[1] += L.y; a[2] += L.z;
     }
     vp.q_regen[queue_push_uniform(&vp.counts[VQ_REGEN])] = slot;
@@ -102,19 +102,16 @@ LJ_D Ray vol_main_ray(const DScene &sc, const VolPath &p) {
 }
 
 // ---- stage: generate (vol_path_tracing.h:509-532) ----
-__global__ void __launch_bounds__(128) k_vol_generate(DScene sc, VolPool vp, int n_upper, int s_end, int ntx, int tile_rank, int tile_world) {
+__global__ void __launch_bounds__(128) k_vol_generate(DScene sc, VolPool vp, int n_upper, int s_end) {
     const int n_regen = min(n_upper, vp.counts[VQ_REGEN]);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_regen; i += gridDim.x * blockDim.x) {
         const int slot = vp.q_regen[i];
         VolPath p = vp.path[slot];
-        const int s = p.sample + vp.K;
-        const int pix = (int)(slot % vp.npix);
-        const int w = sc.camera.width;
-        const int x = pix % w, y = pix / w;
-        bool mine = true;
-        if (tile_world > 0) mine = (((y / 16) * ntx + (x / 16)) % tile_world) == tile_rank;
-        if (s >= s_end || !mine) continue;
-        Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)vp.npix + (unsigned long long)pix);
+        const int s = p.sample + vp.map.K;
+        int pix, x, y;
+        const bool on_film = slot_pixel(vp.map, slot, pix, x, y);
+        if (s >= s_end || !on_film) continue;
+        Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)vp.map.npix_total + (unsigned long long)pix);
         Ray ray = volpath_primary(sc, x, y, rng);
         p.ox = ray.org.x; p.oy = ray.org.y; p.oz = ray.org.z; p.spread = 0;
         p.dx = ray.dir.x; p.dy = ray.dir.y; p.dz = ray.dir.z; p.eta_scale = 1;
@@ -180,7 +177,7 @@ LJ_D void vol_roulette_and_continue(const DScene &sc, const VolPool &vp, int slo
     if (p.bounces >= sc.options.rr_depth) {
         const double rr_prob = lmin(max3((1 / p.eta_scale) * thr), 0.95);
         const double u = pcg_real(rng);
-        if (u > rr_prob) { vol_terminate(vp, slot, mk3(p.rx, p.ry, p.rz)); return; }
+        if (u > rr_prob) { vol_terminate(vp, slot, p.sample, mk3(p.rx, p.ry, p.rz)); return; }
         thr = thr / rr_prob;
     }
     p.tx = thr.x; p.ty = thr.y; p.tz = thr.z;
@@ -192,7 +189,7 @@ LJ_D void vol_roulette_and_continue(const DScene &sc, const VolPool &vp, int slo
 
 LJ_D Pcg32 vol_rng(const VolPool &vp, int slot, const VolPath &p) {
     Pcg32 rng; rng.state = p.rng;
-    rng.inc = (((unsigned long long)p.sample * (unsigned long long)vp.npix + (unsigned long long)(slot % vp.npix)) << 1u) | 1u;
+    rng.inc = (slot_stream(vp.map, slot, p.sample) << 1u) | 1u;
     return rng;
 }
 LJ_D Hit to_hit(const HitRec &hr) {
@@ -260,7 +257,7 @@ __global__ void __launch_bounds__(128, LJ_VOL_TRACK_MIN_BLOCKS) k_vol_track(DSce
             slot = resumed ? q_cont[item] : q_fresh[item - n_cont];
             const VolPath *pp = &vp.path[slot];
             rng.state = pp->rng;
-            rng.inc = (((unsigned long long)pp->sample * (unsigned long long)vp.npix + (unsigned long long)(slot % vp.npix)) << 1u) | 1u;
+            rng.inc = (slot_stream(vp.map, slot, pp->sample) << 1u) | 1u;
             scatter = false; ts.active = false; steps = 0;
             if (NEE) {
                 const VolNee ne = vp.nee[slot];
@@ -336,7 +333,7 @@ __global__ void __launch_bounds__(128, LJ_VOL_MAIN_MIN_BLOCKS) k_vol_main(DScene
             multi = multi * trans_dir_pdf;
         } else {
             if (hit) ray.org = vertex.position;
-            else { vol_terminate(vp, slot, mk3(0.0)); dead = true; }          // :637 returns zero, not the radiance so far
+            else { vol_terminate(vp, slot, p.sample, mk3(0.0)); dead = true; }          // :637 returns zero, not the radiance so far
         }
         __syncwarp(together);
         if (dead) continue;
@@ -346,7 +343,7 @@ __global__ void __launch_bounds__(128, LJ_VOL_MAIN_MIN_BLOCKS) k_vol_main(DScene
             d3 Le = vertex_emission(sc, vertex, -ray.dir);
             if (p.bounces == 0) {
                 rad += thr * Le;
-                vol_terminate(vp, slot, rad);
+                vol_terminate(vp, slot, p.sample, rad);
                 continue;
             }
             PointAndNormal light_point; light_point.position = vertex.position; light_point.normal = vertex.geometry_normal;
@@ -375,7 +372,7 @@ __global__ void __launch_bounds__(128, LJ_VOL_MAIN_MIN_BLOCKS) k_vol_main(DScene
             continue;
         }
         const int max_depth = sc.options.max_depth;
-        if (p.bounces >= max_depth - 1 && max_depth != -1) { vol_terminate(vp, slot, rad); continue; }
+        if (p.bounces >= max_depth - 1 && max_depth != -1) { vol_terminate(vp, slot, p.sample, rad); continue; }
 
         const bool nee_medium = scatter && p.medium != -1;
         if (!nee_medium && !hit) {                                     // nothing to scatter on: straight to the roulette
@@ -549,7 +546,7 @@ __global__ void __launch_bounds__(128, LJ_VOL_FINISH_MIN_BLOCKS) k_vol_finish_su
         d2 bsdf_uv; bsdf_uv.x = pcg_real(rng); bsdf_uv.y = pcg_real(rng);
         const double bsdf_w = pcg_real(rng);
         BSDFSample bs;
-        if (!bsdf_sample(mat, vertex, dir_view, bsdf_uv, bsdf_w, bs)) { vol_terminate(vp, slot, rad); continue; }
+        if (!bsdf_sample(mat, vertex, dir_view, bsdf_uv, bsdf_w, bs)) { vol_terminate(vp, slot, p.sample, rad); continue; }
         const d3 dir_bsdf = bs.dir_out;
         p.dx = dir_bsdf.x; p.dy = dir_bsdf.y; p.dz = dir_bsdf.z;
         if (bs.eta == 0) {
@@ -580,23 +577,14 @@ __global__ void k_vol_reset_stage_queues(int *counts, int parity) {
 }
 __global__ void k_vol_init(VolPool vp, int s_begin) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < vp.capacity; i += (long long)gridDim.x * blockDim.x) {
-        const int k = (int)(i / vp.npix);
+        const int k = (int)(i / vp.map.npix_local);
         VolPath p; memset(&p, 0, sizeof p);
-        p.sample = s_begin + k - vp.K;
+        p.sample = s_begin + k - vp.map.K;
         vp.path[i] = p;
-        vp.accum[3 * i] = 0; vp.accum[3 * i + 1] = 0; vp.accum[3 * i + 2] = 0;
         vp.q_regen[i] = (int)i;
     }
     if (blockIdx.x == 0 && threadIdx.x == 0) vp.counts[VQ_REGEN] = vp.capacity;
 }
-__global__ void k_vol_sum(long long npix, int K, const double *accum, double *sum) {
-    const long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npix * 3) return;
-    double a = 0;
-    for (int k = 0; k < K; k++) a += accum[(size_t)k * npix * 3 + i];
-    sum[i] = a;
-}
-
 template <int KIND>
 void launch_finish(const DScene &d, const VolPool &vp, int n_upper, int grid_cap) {
     int grid = (n_upper + 127) / 128;
@@ -607,12 +595,12 @@ void launch_finish(const DScene &d, const VolPool &vp, int n_upper, int grid_cap
 
 } // namespace
 
-static int ensure_vol_pool(lj_scene *s, int capacity, int K, long long npix, VolPool &vp) {
-    const size_t cap = (size_t)capacity;
+static int ensure_vol_pool(lj_scene *s, const SlotMap &map, VolPool &vp) {
+    const size_t cap = (size_t)map.K * map.npix_local;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     const size_t o_path = take(cap * sizeof(VolPath)), o_nee = take(cap * sizeof(VolNee));
-    const size_t o_hit = take(cap * sizeof(HitRec)), o_nhit = take(cap * sizeof(HitRec)), o_acc = take(cap * 3 * sizeof(double));
+    const size_t o_hit = take(cap * sizeof(HitRec)), o_nhit = take(cap * sizeof(HitRec)), o_acc = take((size_t)map.K0 * map.npix_local * 3 * sizeof(double));
     const size_t o_trk = take(cap * sizeof(VolTrack));
     const size_t o_er = take(cap * sizeof(ExtRec)), o_es = take(cap * sizeof(int));
     const size_t o_qr = take(cap * sizeof(int)), o_qm = take(cap * sizeof(int)), o_qn = take(cap * sizeof(int)), o_qfm = take(cap * sizeof(int));
@@ -624,7 +612,7 @@ static int ensure_vol_pool(lj_scene *s, int capacity, int K, long long npix, Vol
     void *arena = nullptr;
     if (int rc = lj_ctx_arena(s->ctx, off, &arena)) return rc;
     char *b = (char *)arena;
-    vp.capacity = capacity; vp.K = K; vp.npix = npix;
+    vp.capacity = (int)cap; vp.map = map;
     vp.path = (VolPath *)(b + o_path); vp.nee = (VolNee *)(b + o_nee); vp.hit = (HitRec *)(b + o_hit); vp.nee_hit = (HitRec *)(b + o_nhit); vp.track = (VolTrack *)(b + o_trk);
     vp.accum = (double *)(b + o_acc); vp.ext_ray = (ExtRec *)(b + o_er); vp.ext_slot = (int *)(b + o_es);
     vp.q_regen = (int *)(b + o_qr); vp.q_main = (int *)(b + o_qm); vp.q_nee = (int *)(b + o_qn); vp.q_fin_medium = (int *)(b + o_qfm);
@@ -640,30 +628,18 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     const DScene &d = s->d;
     const long long npix = (long long)rl.width * rl.height;
     const int nsamp = rl.s_end - rl.s_begin;
-    bool grid_media = false;            // any heterogeneous medium -> run the tracking kernels
-    {
-        std::vector<lj_medium> media(d.num_media);
-        if (d.num_media) LJ_CUDA(cudaMemcpy(media.data(), d.media, sizeof(lj_medium) * d.num_media, cudaMemcpyDeviceToHost));
-        for (const lj_medium &m : media) grid_media = grid_media || m.kind == LJ_MEDIUM_HETEROGENEOUS;
-    }
+    const bool grid_media = s->grid_media;      // any heterogeneous medium -> run the tracking kernels
     // slots in flight: grid media want many (the iteration count, not the arithmetic, bounds them: each iteration
     // waits for its slowest tracking chain), homogeneous scenes run best when the records stay close to L2 size
     long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (grid_media ? (4LL << 20) : (1LL << 20));
-    int K = (int)((target + npix - 1) / npix);
-    if (K > nsamp) K = nsamp;
-    if (K < 1) K = 1;
-    if (npix * K > 0x3fffffffLL / 4) { lj_set_error("volumetric wavefront: pool too large"); return LJ_EINVAL; }
-    const int capacity = (int)(npix * K);
+    // (a target just below a power of two of sample lanes is rounded UP: K is a power of two, see SlotMap)
+    const SlotMap map = lj_make_slot_map(rl.width, rl.height, rl.s_begin, rl.s_end, rl.p.tile_rank, rl.p.tile_world, target + target / 2);
+    if ((long long)map.npix_local * map.K > 0x3fffffffLL / 4) { lj_set_error("volumetric wavefront: pool too large"); return LJ_EINVAL; }
     VolPool vp;
-    int rc = ensure_vol_pool(s, capacity, K, npix, vp);
+    int rc = ensure_vol_pool(s, map, vp);
     if (rc) return rc;
-
-    bool kind_present[LJ_MAT_KIND_COUNT] = {false};
-    {
-        std::vector<lj_material> mats(d.num_materials);
-        if (d.num_materials) LJ_CUDA(cudaMemcpy(mats.data(), d.materials, sizeof(lj_material) * d.num_materials, cudaMemcpyDeviceToHost));
-        for (const lj_material &m : mats) if (m.kind >= 0 && m.kind < LJ_MAT_KIND_COUNT) kind_present[m.kind] = true;
-    }
+    const int capacity = vp.capacity;
+    const bool *kind_present = s->kind_present;
     auto env_int = [](const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; };
     TraceTuning tune; tune.refill_below = env_int("LJ_REFILL_BELOW", 24); tune.prim_thresh = env_int("LJ_PRIM_THRESH", 8);
     const int track_refill = env_int("LJ_TRACK_REFILL_BELOW", 24);
@@ -678,6 +654,8 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     if (stage_timing) for (auto &e : ev) cudaEventCreate(&e);
 
     LJ_CUDA(cudaMemsetAsync(vp.counts, 0, 64 * sizeof(int)));
+    LJ_CUDA(cudaMemsetAsync(vp.accum, 0, (size_t)map.K0 * map.npix_local * 3 * sizeof(double)));
+    if (map.tile_world > 0) LJ_CUDA(cudaMemsetAsync(dev_sum, 0, sizeof(double) * 3 * (size_t)npix));
     k_vol_init<<<sm * 8, 256>>>(vp, rl.s_begin);
     LJ_CUDA(cudaGetLastError());
     // Queue sizes live on the device and every kernel clamps its range to them, so the host does not have to
@@ -701,7 +679,7 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         const int upper = exact ? n_ext + n_regen : capacity;
         if (stage_timing) cudaEventRecord(ev[0]);
         if (regen_upper > 0) {
-            k_vol_generate<<<grid_for(regen_upper, stage_grid_cap), 128>>>(d, vp, regen_upper, rl.s_end, rl.ntx, rl.p.tile_rank, rl.p.tile_world);
+            k_vol_generate<<<grid_for(regen_upper, stage_grid_cap), 128>>>(d, vp, regen_upper, rl.s_end);
             launches++;
         }
         k_vol_reset<<<1, 32>>>(vp.counts, VQ_REGEN, -1);
@@ -766,11 +744,11 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
             if (n_regen == 0 && n_ext == 0 && n_cont == 0) { finished = true; break; }
         }
     }
-    cudaDeviceSynchronize();            // drains the (empty) iterations still in flight before the ring is freed
+    cudaStreamSynchronize(0);           // drains the (empty) iterations still in flight before the ring is freed
     for (int i = 0; i < depth; i++) cudaEventDestroy(done[i]);
     cudaFreeHost(h_ring);
     if (loop_rc != LJ_OK) return loop_rc;
-    k_vol_sum<<<(unsigned)((npix * 3 + 255) / 256), 256>>>(npix, K, vp.accum, dev_sum);
+    k_slot_sum<<<(unsigned)(((long long)map.npix_local * 3 + 255) / 256), 256>>>(map, vp.accum, dev_sum);
     LJ_CUDA(cudaGetLastError());
     if (counting) {
         unsigned long long h_trav[2];

@@ -18,8 +18,8 @@
 
 namespace {
 
-LJ_D void terminate_path(const WfPool &wp, int slot, d3 radiance) {
-    double *a = wp.accum + 3 * (size_t)slot;
+LJ_D void terminate_path(const WfPool &wp, int slot, int sample, d3 radiance) {
+    double *a = wp.accum + accum_offset(wp.map, slot, sample);
     a[0] += radiance.x; a[1] += radiance.y; a[2] += radiance.z;      // render.cpp:92: radiance += path_tracing(...)
     wp.q_regen[queue_push_uniform(&wp.counts[Q_REGEN])] = slot;
 }
@@ -32,18 +32,26 @@ LJ_D void push_extend(const WfPool &wp, int slot, const Ray &r) {
 }
 
 // ---- stage: generate (path_tracing.h:9-14, render.cpp:88-93 loop head) ----
-__global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n_regen, int s_end, int ntx, int tile_rank, int tile_world) {
+// Counter discipline of an iteration (all kernels of one render run in stream order, so a kernel may zero any counter
+// that neither it nor an earlier unfinished kernel uses): generate zeroes what the previous iteration's shade / shadow /
+// finish stages consumed, extend zeroes the regeneration queue generate has just drained, miss (launched before the
+// shade kernels) zeroes the extension queue extend has just drained.  No host-side reset launches.
+__global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n_upper, int s_end) {
+    const int n_regen = min(n_upper, wp.counts[Q_REGEN]);
+    if (blockIdx.x == 0 && threadIdx.x < Q_COUNT) {
+        const int q = threadIdx.x;
+        if (q == Q_SHADOW || q == Q_FINISH || q == Q_MISS || q >= Q_KIND0) wp.counts[q] = 0;
+        if (q == 0) { wp.counts[W_EXT] = 0; wp.counts[W_SHADOW] = 0; }
+    }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_regen; i += gridDim.x * blockDim.x) {
         int slot = wp.q_regen[i];
         ThrRec tr = wp.thr[slot];
-        int s = tr.sample + wp.K;
-        int pix = (int)(slot % wp.npix);
+        int s = tr.sample + wp.map.K;
+        int pix, x, y;
+        const bool on_film = slot_pixel(wp.map, slot, pix, x, y);
+        if (s >= s_end || !on_film) continue;                   // slot exhausted
         int w = sc.camera.width, h = sc.camera.height;
-        int x = pix % w, y = pix / w;
-        bool mine = true;
-        if (tile_world > 0) mine = (((y / 16) * ntx + (x / 16)) % tile_world) == tile_rank;
-        if (s >= s_end || !mine) continue;                      // slot exhausted
-        Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)wp.npix + (unsigned long long)pix);
+        Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)wp.map.npix_total + (unsigned long long)pix);
         double u_first = pcg_real(rng), u_second = pcg_real(rng);   // right-to-left argument evaluation, see lj_path.cuh
         Ray ray = sample_primary(sc.camera, mk2((x + u_second) / w, (y + u_first) / h));
         RayDiff rd = init_ray_differential(w, h);
@@ -62,35 +70,19 @@ __global__ void __launch_bounds__(128) k_wf_finish(WfPool wp, int n_upper) {
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         int slot = wp.q_finish[i];
         RadRec ra = wp.rad[slot];
-        terminate_path(wp, slot, mk3(ra.rx, ra.ry, ra.rz));
+        terminate_path(wp, slot, wp.thr[slot].sample, mk3(ra.rx, ra.ry, ra.rz));
     }
-}
-
-__global__ void k_wf_reset(int *counts, int a, int b, int c) {
-    if (threadIdx.x == 0) { if (a >= 0) counts[a] = 0; if (b >= 0) counts[b] = 0; if (c >= 0) counts[c] = 0; }
-}
-__global__ void k_wf_reset_kinds(int *counts) {
-    if (threadIdx.x < Q_COUNT - Q_FINISH) counts[Q_FINISH + threadIdx.x] = 0;
-    if (threadIdx.x == 0) { counts[24] = 0; counts[25] = 0; }
 }
 
 __global__ void k_wf_init(WfPool wp, int s_begin) {
     for (long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x; i < wp.capacity; i += (long long)gridDim.x * blockDim.x) {
-        int k = (int)(i / wp.npix);
+        int k = (int)(i / wp.map.npix_local);
         ThrRec tr; tr.tx = tr.ty = tr.tz = 0; tr.p2 = 0; tr.fx = tr.fy = tr.fz = 0; tr.nv = 0;
-        tr.sample = s_begin + k - wp.K;
+        tr.sample = s_begin + k - wp.map.K;
         wp.thr[i] = tr;
-        wp.accum[3 * i] = 0; wp.accum[3 * i + 1] = 0; wp.accum[3 * i + 2] = 0;
         wp.q_regen[i] = (int)i;
     }
-}
-
-__global__ void k_wf_sum(long long npix, int K, const double *accum, double *sum) {
-    long long i = (long long)blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= npix * 3) return;
-    double a = 0;
-    for (int k = 0; k < K; k++) a += accum[(size_t)k * npix * 3 + i];
-    sum[i] = a;
+    if (blockIdx.x == 0 && threadIdx.x == 0) wp.counts[Q_REGEN] = wp.capacity;
 }
 
 } // namespace
@@ -183,9 +175,8 @@ __global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc
         ThrRec tr = wp.thr[slot];
         RadRec ra = wp.rad[slot];
         HitRec hr = wp.hit[slot];
-        int pix = (int)(slot % wp.npix);
         Pcg32 rng; rng.state = ra.rng;
-        rng.inc = (((unsigned long long)tr.sample * (unsigned long long)wp.npix + (unsigned long long)pix) << 1u) | 1u;
+        rng.inc = (slot_stream(wp.map, slot, tr.sample) << 1u) | 1u;
         Ray ray = make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), 0, 0);
         d3 throughput = mk3(tr.tx, tr.ty, tr.tz), radiance = mk3(ra.rx, ra.ry, ra.rz);
         Hit h; h.t = hr.t; h.u = hr.u; h.v = hr.v; h.geom = hr.geom; h.prim = hr.prim; h.ngx = hr.ngx; h.ngy = hr.ngy; h.ngz = hr.ngz;
@@ -228,7 +219,7 @@ __global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc
         bool pushed_shadow = false;
         if (alive) alive = bounce_at_vertex<KIND>(sc, wp, slot, vertex, -ray.dir, rng, throughput, rr, tr, pushed_shadow);
         if (!alive) {
-            if (!pushed_shadow) { terminate_path(wp, slot, radiance); continue; }
+            if (!pushed_shadow) { terminate_path(wp, slot, tr.sample, radiance); continue; }
             // the path ends here but its last NEE term is still in the shadow queue: park the
             // radiance and let the finish stage (after the shadow stage) do the accumulation
             ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
@@ -246,6 +237,7 @@ __global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc
 // ---- stage: miss (path_tracing.h:17-28 and :283-307) ----
 __global__ void __launch_bounds__(128) k_wf_miss(DScene sc, WfPool wp, int n_upper) {
     int n = min(n_upper, wp.counts[Q_MISS]);
+    if (blockIdx.x == 0 && threadIdx.x == 0) wp.counts[Q_EXT] = 0;      // drained by the extend stage; the shade kernels refill it
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         int slot = wp.q_miss[i];
         RayRec rr = wp.ray[slot];
@@ -271,7 +263,7 @@ __global__ void __launch_bounds__(128) k_wf_miss(DScene sc, WfPool wp, int n_upp
                 radiance += throughput * C2 * w2;
             }
         }
-        terminate_path(wp, slot, radiance);
+        terminate_path(wp, slot, tr.sample, radiance);
     }
 }
 
@@ -284,12 +276,12 @@ void launch_shade(const DScene &d, const WfPool &wp, int n_upper, int grid_cap) 
 
 } // namespace
 
-static int ensure_pool(lj_scene *s, int capacity, int K, long long npix, WfPool &wp) {
-    size_t cap = (size_t)capacity;
+static int ensure_pool(lj_scene *s, const SlotMap &map, WfPool &wp) {
+    const size_t cap = (size_t)map.K * map.npix_local;
     size_t off = 0;
     auto take = [&](size_t bytes) { size_t o = off; off += (bytes + 255) & ~(size_t)255; return o; };
     size_t o_ray = take(cap * sizeof(RayRec)), o_thr = take(cap * sizeof(ThrRec)), o_rad = take(cap * sizeof(RadRec));
-    size_t o_hit = take(cap * sizeof(HitRec)), o_acc = take(cap * 3 * sizeof(double));
+    size_t o_hit = take(cap * sizeof(HitRec)), o_acc = take((size_t)map.K0 * map.npix_local * 3 * sizeof(double));
     size_t o_er = take(cap * sizeof(ExtRec)), o_es = take(cap * sizeof(int)), o_sh = take(cap * sizeof(ShadowRec));
     size_t o_qr = take(cap * sizeof(int)), o_qm = take(cap * sizeof(int)), o_qf = take(cap * sizeof(int));
     size_t o_qk[LJ_MAT_KIND_COUNT];
@@ -298,7 +290,7 @@ static int ensure_pool(lj_scene *s, int capacity, int K, long long npix, WfPool 
     void *arena = nullptr;
     if (int rc = lj_ctx_arena(s->ctx, off, &arena)) return rc;
     char *b = (char *)arena;
-    wp.capacity = capacity; wp.K = K; wp.npix = npix;
+    wp.capacity = (int)cap; wp.map = map;
     wp.ray = (RayRec *)(b + o_ray); wp.thr = (ThrRec *)(b + o_thr); wp.rad = (RadRec *)(b + o_rad); wp.hit = (HitRec *)(b + o_hit);
     wp.accum = (double *)(b + o_acc); wp.ext_ray = (ExtRec *)(b + o_er); wp.ext_slot = (int *)(b + o_es);
     wp.shadow = (ShadowRec *)(b + o_sh); wp.q_regen = (int *)(b + o_qr); wp.q_miss = (int *)(b + o_qm); wp.q_finish = (int *)(b + o_qf);
@@ -312,104 +304,123 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     if (!d.bvh8) return lj_render_megakernel(s, rl, dev_sum, st);   // LJ_BVH=2 validation mode: binary tree only
     const long long npix = (long long)rl.width * rl.height;
     const int nsamp = rl.s_end - rl.s_begin;
-    // pool sizing: K slots per pixel, ~8 Mi paths in flight unless the caller says otherwise (sweep 2..16 Mi in
-    // profiles/r01_experiments.md: fewer, larger iterations; sponza is flat from 4 Mi, matpreview gains 13 %)
-    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (8LL << 20);
-    int K = (int)((target + npix - 1) / npix);
-    if (K > nsamp) K = nsamp;
-    if (K < 1) K = 1;
-    if (npix * K > 0x7fffffffLL / 4) { lj_set_error("wavefront: pool too large"); return LJ_EINVAL; }
-    const int capacity = (int)(npix * K);
+    // pool sizing: K sample lanes per owned pixel, ~12 Mi paths in flight unless the caller says otherwise (K is rounded
+    // down to a power of two, see SlotMap; sweep 2..16 Mi in profiles/r01_experiments.md: fewer, larger iterations;
+    // sponza is flat from 4 Mi, matpreview gains 13 % up to 16 Mi)
+    const long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (12LL << 20);
+    const SlotMap map = lj_make_slot_map(rl.width, rl.height, rl.s_begin, rl.s_end, rl.p.tile_rank, rl.p.tile_world, target);
+    if ((long long)map.npix_local * map.K > 0x7fffffffLL / 4) { lj_set_error("wavefront: pool too large"); return LJ_EINVAL; }
     WfPool wp;
-    int rc = ensure_pool(s, capacity, K, npix, wp);
+    int rc = ensure_pool(s, map, wp);
     if (rc) return rc;
+    const int capacity = wp.capacity;
+    const bool *kind_present = s->kind_present;
 
-    // which material kinds exist in this scene (host copy of the kinds, once per render)
-    bool kind_present[LJ_MAT_KIND_COUNT] = {false};
-    {
-        std::vector<lj_material> mats(d.num_materials);
-        if (d.num_materials) LJ_CUDA(cudaMemcpy(mats.data(), d.materials, sizeof(lj_material) * d.num_materials, cudaMemcpyDeviceToHost));
-        for (const lj_material &m : mats) if (m.kind >= 0 && m.kind < LJ_MAT_KIND_COUNT) kind_present[m.kind] = true;
-    }
     const int sm = s->ctx->sm_count;
-    int trace_grid_cap = sm * 16; const int shade_grid_cap = sm * 16;
+    const int shade_grid_cap = sm * 16;
     auto env_int = [](const char *name, int dflt) { const char *v = getenv(name); return v ? atoi(v) : dflt; };
     TraceTuning tune_ext, tune_sh;     // tuning knobs (defaults measured on B200, see profiles/)
     tune_ext.refill_below = env_int("LJ_REFILL_BELOW", 24); tune_ext.prim_thresh = env_int("LJ_PRIM_THRESH", 12);
     tune_sh.refill_below = env_int("LJ_REFILL_BELOW_SHADOW", 24); tune_sh.prim_thresh = env_int("LJ_PRIM_THRESH_SHADOW", 6);
-    const int trace_mult = env_int("LJ_TRACE_GRID_MULT", 16);
-    trace_grid_cap = sm * trace_mult;
+    const int trace_grid_cap = sm * env_int("LJ_TRACE_GRID_MULT", 16);
     const bool trace_iters = getenv("LJ_WF_TRACE") != nullptr;
     const bool stage_timing = (rl.p.flags & 2) != 0 || trace_iters;
     const bool counting = (rl.p.flags & 1) != 0 && d.bvh8 != nullptr;
     unsigned long long *trav = (unsigned long long *)(wp.counts + 32);   // 4 x u64 after the queue counters
-    cudaEvent_t ev[5];
-    if (stage_timing) for (auto &e : ev) cudaEventCreate(&e);
 
-    LJ_CUDA(cudaMemsetAsync(wp.counts, 0, 64 * sizeof(int)));
-    k_wf_init<<<sm * 8, 256>>>(wp, rl.s_begin);
-    LJ_CUDA(cudaGetLastError());
-    int n_regen = capacity, n_ext = 0;
-    unsigned long long launches = 2, rays_primary = 0, rays_ext = 0, rays_shadow = 0;
-    int h_counts[Q_COUNT];
-    auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
-    while (n_regen > 0 || n_ext > 0) {
-        if (stage_timing) cudaEventRecord(ev[0]);
-        if (n_regen > 0) {
-            k_wf_generate<<<grid_for(n_regen, shade_grid_cap), 128>>>(d, wp, n_regen, rl.s_end, rl.ntx, rl.p.tile_rank, rl.p.tile_world);
-            launches++;
-        }
-        k_wf_reset<<<1, 32>>>(wp.counts, Q_REGEN, -1, -1);
-        if (stage_timing) cudaEventRecord(ev[1]);
-        int ext_upper = n_ext + n_regen;
-        lj_wf_launch_extend(d, wp, ext_upper, trav, tune_ext, counting, grid_for(ext_upper, trace_grid_cap));
-        k_wf_reset<<<1, 32>>>(wp.counts, Q_EXT, -1, -1);
-        if (stage_timing) cudaEventRecord(ev[2]);
-        if (kind_present[0]) launch_shade<0>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[1]) launch_shade<1>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[2]) launch_shade<2>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[3]) launch_shade<3>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[4]) launch_shade<4>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[5]) launch_shade<5>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[6]) launch_shade<6>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[7]) launch_shade<7>(d, wp, ext_upper, shade_grid_cap);
-        if (kind_present[8]) launch_shade<8>(d, wp, ext_upper, shade_grid_cap);
-        k_wf_miss<<<grid_for(ext_upper, shade_grid_cap), 128>>>(d, wp, ext_upper);
-        if (stage_timing) cudaEventRecord(ev[3]);
-        lj_wf_launch_shadow(d, wp, ext_upper, trav, tune_sh, counting, grid_for(ext_upper, trace_grid_cap));
-        k_wf_finish<<<grid_for(ext_upper, shade_grid_cap), 128>>>(wp, ext_upper);
-        if (stage_timing) cudaEventRecord(ev[4]);
-        // one readback per iteration: queue sizes for the next one (also the ray counts)
-        LJ_CUDA(cudaMemcpy(h_counts, wp.counts, sizeof h_counts, cudaMemcpyDeviceToHost));
-        k_wf_reset_kinds<<<1, 32>>>(wp.counts);
-        k_wf_reset<<<1, 32>>>(wp.counts, Q_SHADOW, -1, -1);
-        launches += 8;
-        for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
-        int traced = h_counts[Q_MISS];
-        for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) traced += h_counts[Q_KIND0 + k];
-        // rays traced this iteration = hits + misses; the first n_regen-derived ones are primaries
-        int prim_now = traced - n_ext;
-        rays_primary += prim_now > 0 ? prim_now : 0;
-        rays_ext += traced - (prim_now > 0 ? prim_now : 0);
-        rays_shadow += h_counts[Q_SHADOW];
-        if (stage_timing) {
-            float ms;
-            cudaEventElapsedTime(&ms, ev[0], ev[1]); st->generate_ms += ms;
-            cudaEventElapsedTime(&ms, ev[1], ev[2]); st->extend_ms += ms;
-            cudaEventElapsedTime(&ms, ev[2], ev[3]); st->shade_ms += ms;
-            cudaEventElapsedTime(&ms, ev[3], ev[4]); st->shadow_ms += ms;
-        }
-        if (trace_iters) {
-            float ms_e = 0, ms_s = 0, ms_h = 0;
-            if (stage_timing) { cudaEventElapsedTime(&ms_e, ev[1], ev[2]); cudaEventElapsedTime(&ms_s, ev[2], ev[3]); cudaEventElapsedTime(&ms_h, ev[3], ev[4]); }
-            fprintf(stderr, "[wf] iter %llu: traced %d (regen %d) shadow %d -> next ext %d regen %d | extend %.3f shade %.3f shadow %.3f ms\n",
-                    (unsigned long long)st->iterations, traced, n_regen, h_counts[Q_SHADOW], h_counts[Q_EXT], h_counts[Q_REGEN], ms_e, ms_s, ms_h);
-        }
-        n_regen = h_counts[Q_REGEN];
-        n_ext = h_counts[Q_EXT];
-        st->iterations++;
+    // Queue sizes live on the device and every kernel clamps its range to them, so the host does not need them to
+    // launch the next iteration: it sizes grids from the last sizes it has seen (or the pool capacity) and reads the
+    // counters back through a ring of pinned buffers, up to `depth` iterations behind.  Iterations launched after the
+    // one that emptied the pool find empty queues and do nothing (LJ_WF_PIPELINE=1 restores one read-back per iteration).
+    const int depth = trace_iters ? 1 : std::max(1, std::min(8, env_int("LJ_WF_PIPELINE", 4)));
+    int *h_ring = nullptr;
+    LJ_CUDA(cudaMallocHost(&h_ring, sizeof(int) * Q_COUNT * depth));
+    cudaEvent_t done[8], ev[8][5];
+    for (int i = 0; i < depth; i++) {
+        cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
+        if (stage_timing) for (auto &e : ev[i]) cudaEventCreate(&e);
     }
-    k_wf_sum<<<(unsigned)((npix * 3 + 255) / 256), 256>>>(npix, K, wp.accum, dev_sum);
+    auto cleanup = [&]() {
+        for (int i = 0; i < depth; i++) { cudaEventDestroy(done[i]); if (stage_timing) for (auto &e : ev[i]) cudaEventDestroy(e); }
+        cudaFreeHost(h_ring);
+    };
+
+    cudaMemsetAsync(wp.counts, 0, 64 * sizeof(int));
+    cudaMemsetAsync(wp.accum, 0, (size_t)map.K0 * map.npix_local * 3 * sizeof(double));
+    if (map.tile_world > 0) cudaMemsetAsync(dev_sum, 0, sizeof(double) * 3 * (size_t)npix);
+    k_wf_init<<<sm * 8, 256>>>(wp, rl.s_begin);
+    if (cudaGetLastError() != cudaSuccess) { cleanup(); lj_set_error("wavefront: init launch failed"); return LJ_ECUDA; }
+    int n_regen = capacity, n_ext = 0;      // queue sizes after the last retired iteration
+    unsigned long long launches = 2, rays_primary = 0, rays_ext = 0, rays_shadow = 0;
+    unsigned long long launched = 0, retired = 0;
+    auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
+    bool finished = false;
+    int loop_rc = LJ_OK;
+    while (!finished) {
+        const bool exact = launched == retired;          // nothing in flight: the sizes are the true ones
+        const int regen_upper = exact ? n_regen : capacity;
+        const int upper = exact ? n_ext + n_regen : capacity;
+        const int ring_slot = (int)(launched % depth);
+        cudaEvent_t *e = ev[ring_slot];
+        if (stage_timing) cudaEventRecord(e[0]);
+        k_wf_generate<<<grid_for(regen_upper, shade_grid_cap), 128>>>(d, wp, regen_upper, rl.s_end);
+        if (stage_timing) cudaEventRecord(e[1]);
+        lj_wf_launch_extend(d, wp, upper, trav, tune_ext, counting, grid_for(upper, trace_grid_cap));
+        if (stage_timing) cudaEventRecord(e[2]);
+        k_wf_miss<<<grid_for(upper, shade_grid_cap), 128>>>(d, wp, upper);
+        if (kind_present[0]) launch_shade<0>(d, wp, upper, shade_grid_cap);
+        if (kind_present[1]) launch_shade<1>(d, wp, upper, shade_grid_cap);
+        if (kind_present[2]) launch_shade<2>(d, wp, upper, shade_grid_cap);
+        if (kind_present[3]) launch_shade<3>(d, wp, upper, shade_grid_cap);
+        if (kind_present[4]) launch_shade<4>(d, wp, upper, shade_grid_cap);
+        if (kind_present[5]) launch_shade<5>(d, wp, upper, shade_grid_cap);
+        if (kind_present[6]) launch_shade<6>(d, wp, upper, shade_grid_cap);
+        if (kind_present[7]) launch_shade<7>(d, wp, upper, shade_grid_cap);
+        if (kind_present[8]) launch_shade<8>(d, wp, upper, shade_grid_cap);
+        if (stage_timing) cudaEventRecord(e[3]);
+        lj_wf_launch_shadow(d, wp, upper, trav, tune_sh, counting, grid_for(upper, trace_grid_cap));
+        k_wf_finish<<<grid_for(upper, shade_grid_cap), 128>>>(wp, upper);
+        if (stage_timing) cudaEventRecord(e[4]);
+        cudaMemcpyAsync(h_ring + ring_slot * Q_COUNT, wp.counts, sizeof(int) * Q_COUNT, cudaMemcpyDeviceToHost);
+        cudaEventRecord(done[ring_slot]);
+        launches += 5;
+        for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
+        launched++;
+        // retire what has completed; block only when the ring is full
+        while (retired < launched) {
+            const int rs = (int)(retired % depth);
+            if (launched - retired < (unsigned long long)depth && cudaEventQuery(done[rs]) == cudaErrorNotReady) break;
+            const cudaError_t ce = cudaEventSynchronize(done[rs]);
+            if (ce != cudaSuccess) { lj_set_error("wavefront iteration failed: %s", cudaGetErrorString(ce)); loop_rc = LJ_ECUDA; finished = true; break; }
+            const int *h_counts = h_ring + rs * Q_COUNT;
+            int traced = h_counts[Q_MISS];
+            for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) traced += h_counts[Q_KIND0 + k];
+            // rays traced this iteration = hits + misses; all but the n_ext carried over are primaries
+            const int prim_now = traced - n_ext > 0 ? traced - n_ext : 0;
+            rays_primary += prim_now; rays_ext += traced - prim_now;
+            rays_shadow += h_counts[Q_SHADOW];
+            float ms_g = 0, ms_e = 0, ms_s = 0, ms_h = 0;
+            if (stage_timing) {
+                cudaEventElapsedTime(&ms_g, ev[rs][0], ev[rs][1]); cudaEventElapsedTime(&ms_e, ev[rs][1], ev[rs][2]);
+                cudaEventElapsedTime(&ms_s, ev[rs][2], ev[rs][3]); cudaEventElapsedTime(&ms_h, ev[rs][3], ev[rs][4]);
+                st->generate_ms += ms_g; st->extend_ms += ms_e; st->shade_ms += ms_s; st->shadow_ms += ms_h;
+            }
+            if (trace_iters)
+                fprintf(stderr, "[wf] iter %llu: traced %d (regen %d) shadow %d -> next ext %d regen %d | extend %.3f shade %.3f shadow %.3f ms\n",
+                        (unsigned long long)st->iterations, traced, n_regen, h_counts[Q_SHADOW], h_counts[Q_EXT], h_counts[Q_REGEN], ms_e, ms_s, ms_h);
+            n_regen = h_counts[Q_REGEN];
+            n_ext = h_counts[Q_EXT];
+            st->iterations++;
+            retired++;
+            // (slots whose samples are used up sit in the regeneration queue once more: that iteration generates
+            //  nothing, extend zeroes the queue, and the counters come back empty)
+            if (n_ext == 0 && n_regen == 0) { finished = true; break; }
+        }
+    }
+    cudaStreamSynchronize(0);           // drains the (empty) iterations still in flight before the ring is freed
+    cleanup();
+    if (loop_rc != LJ_OK) return loop_rc;
+    k_slot_sum<<<(unsigned)(((long long)map.npix_local * 3 + 255) / 256), 256>>>(map, wp.accum, dev_sum);
     LJ_CUDA(cudaGetLastError());
     if (counting) {
         unsigned long long h_trav[4];
@@ -418,7 +429,6 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         st->shadow_nodes_visited = h_trav[2]; st->shadow_prims_tested = h_trav[3];
     }
     launches++;
-    if (stage_timing) for (auto &e : ev) cudaEventDestroy(e);
     st->kernel_launches += launches;
     st->rays_primary += rays_primary; st->rays_extension += rays_ext; st->rays_shadow += rays_shadow;
     st->samples = (uint64_t)npix * (uint64_t)nsamp;

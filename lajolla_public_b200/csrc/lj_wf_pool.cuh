@@ -13,10 +13,10 @@ struct __align__(16) RadRec { double rx, ry, rz; unsigned long long rng; };     
 struct __align__(16) ShadowRec { RayF ray; double cx, cy, cz; int slot, _pad; };             // 64 B
 
 struct WfPool {
-    int capacity, K;
-    long long npix;
+    int capacity;               // = map.K * map.npix_local slots
+    SlotMap map;                // slot -> pixel / sample lane / accumulator (lj_wave_common.cuh)
     RayRec *ray; ThrRec *thr; RadRec *rad; HitRec *hit;
-    double *accum;              // 3 per slot
+    double *accum;              // 3 * K0 per local pixel, see SlotMap
     ExtRec *ext_ray; int *ext_slot;
     ShadowRec *shadow;
     int *q_regen, *q_miss, *q_finish, *q_kind[LJ_MAT_KIND_COUNT];

@@ -32,6 +32,7 @@ namespace {
 template <bool COUNT>
 __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_extend(DScene sc, WfPool wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune) {
     const int n = min(n_upper, wp.counts[Q_EXT]);
+    if (blockIdx.x == 0 && threadIdx.x == 0) wp.counts[Q_REGEN] = 0;    // drained by the generate stage (see k_wf_generate)
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
     tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
