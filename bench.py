@@ -13,6 +13,8 @@ One "step" = one render pass of SPP_PER_STEP samples per pixel of scenes/sponza/
           on all host cores, on a bounded spp sample of the same workload.
 N > 1 (torchrun): the scene is replicated, rank r renders the spp slice [r*S, (r+1)*S) of every
 pixel (weak scaling: per-GPU work fixed) and the f64 radiance sums are all-reduced over NCCL.
+The same line carries a `strong` block: FIXED total work (64 and 1024 spp of the same scene) split over the N GPUs by
+the library's own multi-device context (lj_init_devices), with the 1-GPU time of the same workload beside it.
 """
 import argparse
 import json
@@ -153,10 +155,12 @@ def gpu_arm(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the render path has no CPU fallback")
     torch.cuda.set_device(local)
+    cpu_group = None
     if world > 1:
-        if not os.environ.get("LJ_KEEP_NCCL_DEBUG"):
-            os.environ["NCCL_DEBUG"] = "WARN"      # NCCL's version banner goes to stdout; stdout carries the ONE JSON line
+        # (NCCL_DEBUG is left as the launcher set it: main() has already moved fd 1 to stderr, so NCCL's banner and
+        #  rank lines cannot reach the JSON line)
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+        cpu_group = dist.new_group(backend="gloo")      # host-side barrier that leaves the GPUs idle (strong block)
     dev = torch.device("cuda", local)
 
     blob = find_blob()
@@ -235,6 +239,16 @@ def gpu_arm(args):
         e2e_s = float(tm[0])
     e2e_value = float(te[1]) / e2e_s * 1e-6
 
+    # ---- fixed-work (strong) scaling through the library's own multi-device context, rank 0 drives all N GPUs ----
+    strong = None
+    torch.cuda.synchronize()
+    if cpu_group is not None:
+        dist.barrier(group=cpu_group)
+    if rank == 0 and not args.no_strong:
+        strong = strong_block(gpu, scene, desc, world, args)
+    if cpu_group is not None:
+        dist.barrier(group=cpu_group)
+
     if rank == 0:
         peaks = {}
         try:
@@ -252,7 +266,7 @@ def gpu_arm(args):
                            "l2": "256 MiB buffer written between timed steps (L2 flush)", "partition": f"spp slices x{world}, NCCL all-reduce of f64 sums"},
                 "clocks": sampler.summary(), "gpu_launches": int(launches),
                 "e2e": {"value": e2e_value, "unit": "Mrays/s", "h2d_bytes_per_step": desc.nbytes, "d2h_bytes_per_step": h * w * 3 * 4},
-                "roofline": roof}
+                "roofline": roof, "strong": strong}
         if world == 1 and not args.no_cpu_baseline:
             cores = host_cores()
             probe = run_reference_sample(1, cores)
@@ -266,6 +280,63 @@ def gpu_arm(args):
     scene.close(); gpu.close()
     if world > 1:
         dist.destroy_process_group()
+
+
+def strong_block(gpu1, scene1, desc, n, args):
+    """Fixed TOTAL work split over the N GPUs of the box by the library itself (lj_init_devices: per-device host threads,
+    tile or sample-slice partition, one ncclReduce -- lajolla_public_b200/csrc/lj_multi.cu): sponza at the shipped 64 spp
+    and at 1024 spp.  Every entry: wall-clock ms of the synchronous lj_render_device call (best of `reps`), the device
+    time the library reports (slowest device's CUDA-event time + the reduce), the 1-GPU time of the same workload
+    measured in this run, and e2e_ms = scene upload + BVH build on every device + render + host image.
+    image_check = max |N-way f32 image - 1-GPU f32 image| on identical streams (0 for tiles by construction)."""
+    import numpy as np
+    import torch
+    from lajolla_public_b200 import LajollaGPU, RenderParams, RNG_SAMPLE_STREAMS, PARTITION_TILES, PARTITION_SPP
+    w, h = scene1.width, scene1.height
+    sums = torch.zeros(h * w * 3, dtype=torch.float64, device="cuda:0")
+    out = {"n_gpus": n, "driver": "lj_init_devices (one process, one host thread per GPU, ncclReduce)", "runs": []}
+    multi = LajollaGPU(list(range(n))) if n > 1 else gpu1
+    sceneN = multi.scene_from_desc(desc) if n > 1 else scene1
+    try:
+        for total_spp, reps in ((64, 3), (args.strong_spp, 1)):
+            def timed(sc, rp, reps=reps):
+                best, st = None, None
+                for _ in range(reps):
+                    torch.cuda.synchronize()
+                    t0 = time.perf_counter()
+                    st = sc.render_into_device(sums.data_ptr(), rp)
+                    dt = (time.perf_counter() - t0) * 1e3
+                    best = dt if best is None else min(best, dt)
+                return best, st
+            rp1 = RenderParams(spp=total_spp, rng_mode=RNG_SAMPLE_STREAMS)
+            timed(scene1, rp1, 1)                                  # warm the pool for this spp
+            ms1, st1 = timed(scene1, rp1)
+            ref_img, _ = scene1.render(rp1)
+            for part, pname in ((PARTITION_TILES, "tiles"), (PARTITION_SPP, "spp")):
+                if n == 1 and part == PARTITION_SPP:
+                    continue
+                rp = RenderParams(spp=total_spp, rng_mode=RNG_SAMPLE_STREAMS, partition=part)
+                timed(sceneN, rp, 1)
+                ms, st = timed(sceneN, rp)
+                img, _ = sceneN.render(rp)
+                t0 = time.perf_counter()
+                sc2 = multi.scene_from_desc(desc)
+                img2, st2 = sc2.render(rp)
+                sc2.close()
+                e2e_ms = (time.perf_counter() - t0) * 1e3
+                out["runs"].append({"total_spp": total_spp, "partition": pname if n > 1 else "none", "ms": ms, "device_ms": st.render_ms,
+                                    "reduce_ms": st.reduce_ms, "device_ms_min": st.device_ms_min, "device_ms_max": st.device_ms_max,
+                                    "one_gpu_ms": ms1, "speedup": ms1 / ms, "efficiency": ms1 / ms / n,
+                                    "mrays_per_s": st.rays / ms * 1e-3, "msamples_per_s": w * h * total_spp / ms * 1e-3,
+                                    "e2e_ms": e2e_ms, "bvh_build_ms": st2.bvh_build_ms, "upload_ms": st2.upload_ms,
+                                    "iterations": int(st.iterations), "launches": int(st.kernel_launches),
+                                    "rays": int(st.rays), "rays_one_gpu": int(st1.rays),
+                                    "image_check": float(np.abs(img.astype(np.float64) - ref_img).max()),
+                                    "image_bit_identical": bool(np.array_equal(img.view(np.uint32), ref_img.view(np.uint32)))})
+    finally:
+        if n > 1:
+            sceneN.close(); multi.close()
+    return out
 
 
 def roofline_block(scene, rp, stage, rays_by_type, iterations, peak, which, scratch_ptr):
@@ -330,6 +401,8 @@ def main():
     ap.add_argument("--spp", type=int, default=SPP_PER_STEP)
     ap.add_argument("--engine", default="wavefront")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-strong", action="store_true", help="skip the fixed-work (strong scaling) block")
+    ap.add_argument("--strong-spp", type=int, default=1024)
     args = ap.parse_args()
     if args.impl == "reference":
         reference_arm(args)

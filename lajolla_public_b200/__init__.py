@@ -8,8 +8,8 @@ device and the built shared library.
 """
 from .api import (LajollaGPU, Scene, RenderParams, Stats, LjError, lib_path, load_library,
                   read_pfm, write_pfm, RNG_TILE_STREAMS, RNG_SAMPLE_STREAMS,
-                  ENGINE_WAVEFRONT, ENGINE_MEGAKERNEL)
+                  ENGINE_WAVEFRONT, ENGINE_MEGAKERNEL, PARTITION_AUTO, PARTITION_TILES, PARTITION_SPP)
 
 __all__ = ["LajollaGPU", "Scene", "RenderParams", "Stats", "LjError", "lib_path", "load_library",
            "read_pfm", "write_pfm", "RNG_TILE_STREAMS", "RNG_SAMPLE_STREAMS",
-           "ENGINE_WAVEFRONT", "ENGINE_MEGAKERNEL"]
+           "ENGINE_WAVEFRONT", "ENGINE_MEGAKERNEL", "PARTITION_AUTO", "PARTITION_TILES", "PARTITION_SPP"]

@@ -8,6 +8,7 @@ RNG_TILE_STREAMS = 0     # mode A: render.cpp:82 per-tile pcg32 streams (tile-se
 RNG_SAMPLE_STREAMS = 1   # mode B: per-(pixel,sample) streams
 ENGINE_WAVEFRONT = 0
 ENGINE_MEGAKERNEL = 1
+PARTITION_AUTO, PARTITION_TILES, PARTITION_SPP = 0, 1, 2   # lj_render_params.partition (multi-device contexts)
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
 
@@ -25,7 +26,8 @@ class RenderParams(C.Structure):
     _fields_ = [("spp", C.c_int32), ("rng_mode", C.c_int32), ("engine", C.c_int32),
                 ("sample_begin", C.c_int32), ("sample_end", C.c_int32),
                 ("tile_rank", C.c_int32), ("tile_world", C.c_int32),
-                ("max_depth_override", C.c_int32), ("paths_in_flight", C.c_int32), ("flags", C.c_int32)]
+                ("max_depth_override", C.c_int32), ("paths_in_flight", C.c_int32), ("flags", C.c_int32),
+                ("partition", C.c_int32)]
 
     def __init__(self, **kw):
         super().__init__()
@@ -42,7 +44,9 @@ class Stats(C.Structure):
                 ("kernel_launches", C.c_uint64), ("extend_ms", C.c_double), ("shadow_ms", C.c_double),
                 ("shade_ms", C.c_double), ("generate_ms", C.c_double), ("bvh_nodes", C.c_uint64),
                 ("bvh_prims", C.c_uint64), ("shadow_nodes_visited", C.c_uint64), ("shadow_prims_tested", C.c_uint64),
-                ("iterations", C.c_uint64), ("tables_build_ms", C.c_double)]
+                ("iterations", C.c_uint64), ("tables_build_ms", C.c_double),
+                ("n_devices", C.c_int32), ("partition", C.c_int32), ("reduce_ms", C.c_double),
+                ("device_ms_min", C.c_double), ("device_ms_max", C.c_double)]
 
     @property
     def rays(self):
@@ -65,7 +69,7 @@ RAY_DTYPE = np.dtype([("org", "<f4", 3), ("tnear", "<f4"), ("dir", "<f4", 3), ("
 HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("geom_id", "<i4"), ("prim_id", "<i4"), ("ng", "<f4", 3)])
 
 # every symbol include/lajolla_gpu.h declares
-ABI_SYMBOLS = ["lj_init", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", "lj_render", "lj_render_device",
+ABI_SYMBOLS = ["lj_init", "lj_init_devices", "lj_ctx_device_count", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", "lj_render", "lj_render_device",
                "lj_intersect_batch", "lj_scene_info", "lj_last_error", "lj_scene_desc_save", "lj_scene_desc_load",
                "lj_scene_desc_free", "lj_scene_desc_pin", "lj_image_encoded_size", "lj_image_encode", "lj_image_write",
                "lj_accum_finalize", "lj_accum_encode", "lj_accum_write", "lj_accum_save", "lj_accum_load",
@@ -116,6 +120,8 @@ def load_library():
     lib = C.CDLL(p)
     lib.lj_last_error.restype = C.c_char_p
     lib.lj_init.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
+    lib.lj_init_devices.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+    lib.lj_ctx_device_count.argtypes = [C.c_void_p]
     lib.lj_shutdown.argtypes = [C.c_void_p]
     lib.lj_shutdown.restype = None
     lib.lj_scene_create.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
@@ -159,13 +165,20 @@ def _check(lib, rc, what):
 
 
 class LajollaGPU:
-    """One context per CUDA device (lj_init / lj_shutdown)."""
+    """One context per CUDA device (lj_init / lj_shutdown), or one over several devices of the box
+    (lj_init_devices: `device` a list of ordinals, or "all")."""
 
     def __init__(self, device=0):
         self.lib = load_library()
         self.handle = C.c_void_p()
-        _check(self.lib, self.lib.lj_init(int(device), C.byref(self.handle)), "lj_init")
+        if isinstance(device, (list, tuple)) or device == "all":
+            ids = [] if device == "all" else [int(d) for d in device]
+            arr = (C.c_int * max(len(ids), 1))(*ids)
+            _check(self.lib, self.lib.lj_init_devices(arr if ids else None, len(ids), C.byref(self.handle)), "lj_init_devices")
+        else:
+            _check(self.lib, self.lib.lj_init(int(device), C.byref(self.handle)), "lj_init")
         self.device = device
+        self.n_devices = int(self.lib.lj_ctx_device_count(self.handle))
 
     def load_scene(self, blob_path, res=None, spp=None, integrator=None):
         return Scene(self, blob_path, res=res, spp=spp, integrator=integrator)

@@ -264,6 +264,17 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
         lj_set_error("BVH build failed: %s", berr);
         cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return LJ_ECUDA;
     }
+    // Trav8 pushes at most two entries per level it descends (the rest of the node group and a postponed primitive
+    // group, lj_traverse8.cuh), and drops work when its stack is full: a tree deeper than half the stack is refused
+    // here instead of losing hits silently.  (PLOC trees of the shipped scenes: 6-9 levels; limit 16.)
+    {
+        int max_levels = LJ_BVH8_STACK / 2;
+        if (const char *e = getenv("LJ_BVH8_MAX_LEVELS")) max_levels = atoi(e);      // test hook
+        if (s->bvh.bvh8 && s->bvh.levels8 > max_levels) {
+            lj_set_error("BVH is %d levels deep; the traversal stack (%d entries) covers %d levels", s->bvh.levels8, LJ_BVH8_STACK, max_levels);
+            cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return LJ_EUNSUPPORTED;
+        }
+    }
     cudaEventRecord(e2);
     cudaEventSynchronize(e2);
     d.num_tris = bi.num_tris; d.num_spheres = bi.num_spheres; d.num_prims = s->bvh.num_prims;

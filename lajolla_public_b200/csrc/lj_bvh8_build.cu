@@ -219,6 +219,7 @@ int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left,
     }
     out.num_bvh8 = h_counters[0];
     out.num_slots8 = h_counters[1];
+    out.levels8 = levels;
     lj_free(counters); lj_free(q0); lj_free(q1);
     if (out.num_slots8 != n) { snprintf(err, 256, "bvh8 collapse lost primitives: %d of %d", out.num_slots8, n); return -1; }
     return 0;

@@ -19,6 +19,7 @@ struct BvhBuildOutput {
     Bvh8Node *bvh8; int num_bvh8;
     float4 *tri_verts8;         // primitive slots in 8-wide-tree order
     int num_slots8;
+    int levels8;                // depth of the 8-wide tree (levels of inner nodes), checked against the traversal stack
 };
 
 int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err /* >= 256 bytes */);

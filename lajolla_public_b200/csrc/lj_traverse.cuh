@@ -210,6 +210,7 @@ LJ_D bool traverse_bvh2(const DScene &sc, const RayF &r, Hit *hit_out) {
         }
         bool hl = tl != INF, hr = tr != INF;
         if (hl && hr) {
+            if (sp == 64) __trap();      // binary tree deeper than the stack (validation mode LJ_BVH=2 only): fail loudly, never drop a subtree
             if (tl <= tr) { stack[sp++] = right; node = left; }
             else { stack[sp++] = left; node = right; }
         } else if (hl) node = left;

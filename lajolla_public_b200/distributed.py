@@ -98,7 +98,8 @@ def render_distributed(render_fn, width, height, spp, kind="spp", rank=None, wor
     if part.local_spp > 0:
         stats = render_fn(part, sums)
     reduce_sums(sums, world, root)
-    image = (sums / float(spp)).to(torch.float32).reshape(height, width, 3)
+    # render.cpp:94 divides by multiplying with the reciprocal (vector.h:193-197), and so does k_finalize
+    image = (sums * (1.0 / float(spp))).to(torch.float32).reshape(height, width, 3)
     return image, stats
 
 

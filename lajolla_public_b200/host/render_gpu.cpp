@@ -11,7 +11,10 @@
 //   LJ_RNG_MODE=A|B   A = per-tile pcg32 streams of render.cpp:82 (tile-serial, for
 //                     path-level parity); B = per-(pixel,sample) streams (default).
 //   LJ_ENGINE=wavefront|megakernel     (default wavefront)
-//   LJ_DEVICE=<cuda ordinal>           (default 0)
+//   LJ_DEVICE=<ordinal>[,<ordinal>...]  devices to render on (default: EVERY visible device -- the scene is
+//                     replicated, the render is split by tiles, the sums are added with one NCCL reduce;
+//                     the reference's counterpart is parallel_init(num_threads), main.cpp:31)
+//   LJ_PARTITION=tiles|spp             multi-device split (default tiles: bit-identical to one device)
 //   LJ_SPP=<n>                         override sampleCount
 //   LJ_SAVE_SCENE=<file.ljs>           also write the flattened scene blob
 //   LJ_STATS=1                         print lj_stats to stderr
@@ -26,6 +29,7 @@
 #include <cstdlib>
 #include <cstring>
 #include <string>
+#include <vector>
 
 static lj_ctx *g_ctx = nullptr;
 
@@ -35,8 +39,16 @@ static void check(int rc, const char *what) {
 
 lj_ctx *lj_host_ctx() {
     if (!g_ctx) {
-        int dev = getenv("LJ_DEVICE") ? atoi(getenv("LJ_DEVICE")) : 0;
-        check(lj_init(dev, &g_ctx), "lj_init");
+        std::vector<int> ids;
+        if (const char *e = getenv("LJ_DEVICE")) {
+            for (const char *p = e; *p;) {
+                char *end; long v = strtol(p, &end, 10);
+                if (end == p) break;
+                ids.push_back((int)v);
+                p = *end == ',' ? end + 1 : end;
+            }
+        }
+        check(lj_init_devices(ids.empty() ? nullptr : ids.data(), (int)ids.size(), &g_ctx), "lj_init_devices");
     }
     return g_ctx;
 }
@@ -64,9 +76,9 @@ Image3 render(const Scene &scene) {
     if (rc != LJ_OK) { std::string msg = lj_last_error(); lj_scene_destroy(gs); Error("lj_render failed: " + msg); }
     if (getenv("LJ_STATS")) {
         uint64_t rays = st.rays_primary + st.rays_extension + st.rays_shadow;
-        fprintf(stderr, "[lajolla_b200] render %.3f ms, bvh build %.3f ms, upload %.3f ms, %llu samples (%.2f Msamples/s), "
+        fprintf(stderr, "[lajolla_b200] %d device(s), render %.3f ms (reduce %.3f ms), bvh build %.3f ms, upload %.3f ms, %llu samples (%.2f Msamples/s), "
                         "%llu rays (%.2f Mrays/s), %llu launches\n",
-                st.render_ms, st.bvh_build_ms, st.upload_ms, (unsigned long long)st.samples,
+                st.n_devices, st.render_ms, st.reduce_ms, st.bvh_build_ms, st.upload_ms, (unsigned long long)st.samples,
                 st.samples / st.render_ms * 1e-3, (unsigned long long)rays, rays / st.render_ms * 1e-3,
                 (unsigned long long)st.kernel_launches);
     }

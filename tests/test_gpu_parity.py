@@ -43,7 +43,10 @@ def load_case(gpu, manifest, name):
 # stated 1-spp pixel-match bars per scene (mode A = reference tile streams, mode B = per-sample streams)
 BARS = {"cbox": 0.99, "veach_mi": 0.99, "sponza": 0.99, "matpreview": 0.95, "simple_sphere": 0.99, "pixel_filter_test": 0.99,
         "disney_diffuse": 0.95, "disney_metal": 0.95, "disney_glass": 0.95, "disney_clearcoat": 0.95, "disney_sheen": 0.95,
-        "disney_bsdf": 0.95}
+        "disney_bsdf": 0.95,
+        # Box / Tent pixel filters (filters/box.inl, tent.inl): pixel_filter_test.xml with the <rfilter> variants it keeps
+        # commented out (:23-24), default widths and explicit ones
+        "pixel_filter_box": 0.99, "pixel_filter_tent": 0.99, "pixel_filter_box3": 0.99, "pixel_filter_tent3": 0.99}
 PATH_SCENES = list(BARS)
 
 
