@@ -102,7 +102,6 @@ FILTER_CASES = [
 # ---- round 2: ray-cast seam against the reference's intersect() / occluded() (ref_driver hits) ----
 SEAM_CASES = [
     ("cbox_small", "cbox/cbox.xml", (128, 128), True),
-    ("cbox", "cbox/cbox.xml", None, False),
     ("veach_mi", "veach_mi/mi.xml", None, False),
     ("sponza", "sponza/sponza.xml", None, False),
     ("matpreview", "matpreview/matpreview.xml", None, False),
