@@ -37,6 +37,7 @@ int lj_init_single(int device_id, lj_ctx **out) {
     LJ_CUDA(cudaSetDevice(device_id));
     lj_ctx *c = new lj_ctx();
     c->device = device_id; c->wf_pool = nullptr; c->wf_pool_bytes = 0; c->group = nullptr;
+    c->h_ring = nullptr; c->ring_ready = false;
     {   // keep freed blocks in the device's default memory pool (see lj_alloc.h)
         cudaMemPool_t pool;
         LJ_CUDA(cudaDeviceGetDefaultMemPool(&pool, device_id));
@@ -52,9 +53,24 @@ void lj_shutdown_single(lj_ctx *ctx) {
     cudaSetDevice(ctx->device);
     if (ctx->wf_pool) lj_free(ctx->wf_pool);
     cudaDeviceSynchronize();
+    if (ctx->ring_ready) {
+        for (int i = 0; i < LJ_RING_DEPTH; i++) { cudaEventDestroy(ctx->ring_done[i]); for (auto &e : ctx->ring_ev[i]) cudaEventDestroy(e); }
+        cudaFreeHost(ctx->h_ring);
+    }
     cudaMemPool_t pool;
     if (cudaDeviceGetDefaultMemPool(&pool, ctx->device) == cudaSuccess) cudaMemPoolTrimTo(pool, 0);   // hand the cached blocks back
     delete ctx;
+}
+
+int lj_ctx_ring(lj_ctx *ctx) {
+    if (ctx->ring_ready) return LJ_OK;
+    LJ_CUDA(cudaMallocHost(&ctx->h_ring, sizeof(int) * LJ_RING_INTS * LJ_RING_DEPTH));
+    for (int i = 0; i < LJ_RING_DEPTH; i++) {
+        LJ_CUDA(cudaEventCreateWithFlags(&ctx->ring_done[i], cudaEventDisableTiming));
+        for (auto &e : ctx->ring_ev[i]) LJ_CUDA(cudaEventCreate(&e));
+    }
+    ctx->ring_ready = true;
+    return LJ_OK;
 }
 
 int lj_ctx_arena(lj_ctx *ctx, size_t bytes, void **out) {

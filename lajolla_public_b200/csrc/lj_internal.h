@@ -14,11 +14,19 @@ struct lj_ctx {
     // wavefront path-slot arena: grown on demand, shared by every scene of the context (renders are
     // synchronous and the ABI is single-threaded per context), freed by lj_shutdown
     void *wf_pool; size_t wf_pool_bytes;
+    // read-back ring of the wavefront engines (pinned host buffer + events), created once per context: creating
+    // them per render cost more than a small render itself
+    int *h_ring;                       // LJ_RING_DEPTH x LJ_RING_INTS ints, pinned
+    cudaEvent_t ring_done[8];          // no-timing events, one per ring slot
+    cudaEvent_t ring_ev[8][5];         // timing events per ring slot (stage times, lj_render_params.flags bit1)
+    bool ring_ready;
     // multi-device contexts (lj_init_devices, lj_multi.cu): the per-device contexts, worker threads and NCCL
     // communicators; null for a one-device context.  `this` is then only the handle and mirrors device 0.
     LjDeviceGroup *group;
 };
 int lj_ctx_arena(lj_ctx *ctx, size_t bytes, void **out);
+enum { LJ_RING_DEPTH = 8, LJ_RING_INTS = 64 };
+int lj_ctx_ring(lj_ctx *ctx);          // creates the ring on first use
 
 struct lj_scene {
     lj_ctx *ctx;

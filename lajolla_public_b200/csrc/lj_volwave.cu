@@ -663,10 +663,10 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     // capacity) and reads the counts back through a ring of pinned buffers, `depth` iterations behind.  The
     // iterations launched after the one that emptied the pool find empty queues and do nothing.
     const int depth = stage_timing ? 1 : std::max(1, std::min(8, env_int("LJ_WF_PIPELINE", 4)));
-    int *h_ring = nullptr;
-    LJ_CUDA(cudaMallocHost(&h_ring, sizeof(int) * VT_END * depth));
-    cudaEvent_t done[8];
-    for (int i = 0; i < depth; i++) cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
+    static_assert(VT_END <= LJ_RING_INTS, "ring slot too small for the queue counters");
+    if ((rc = lj_ctx_ring(s->ctx)) != LJ_OK) return rc;
+    int *h_ring = s->ctx->h_ring;
+    cudaEvent_t *done = s->ctx->ring_done;
     int n_regen = capacity, n_ext = 0, n_cont = 0;  // sizes after the last retired iteration (n_cont: suspended segments)
     unsigned long long launches = 2, rays_primary = 0, rays_ext = 0;
     unsigned long long launched = 0, retired = 0;
@@ -745,8 +745,6 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         }
     }
     cudaStreamSynchronize(0);           // drains the (empty) iterations still in flight before the ring is freed
-    for (int i = 0; i < depth; i++) cudaEventDestroy(done[i]);
-    cudaFreeHost(h_ring);
     if (loop_rc != LJ_OK) return loop_rc;
     k_slot_sum<<<(unsigned)(((long long)map.npix_local * 3 + 255) / 256), 256>>>(map, vp.accum, dev_sum);
     LJ_CUDA(cudaGetLastError());

@@ -333,17 +333,12 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     // counters back through a ring of pinned buffers, up to `depth` iterations behind.  Iterations launched after the
     // one that emptied the pool find empty queues and do nothing (LJ_WF_PIPELINE=1 restores one read-back per iteration).
     const int depth = trace_iters ? 1 : std::max(1, std::min(8, env_int("LJ_WF_PIPELINE", 4)));
-    int *h_ring = nullptr;
-    LJ_CUDA(cudaMallocHost(&h_ring, sizeof(int) * Q_COUNT * depth));
-    cudaEvent_t done[8], ev[8][5];
-    for (int i = 0; i < depth; i++) {
-        cudaEventCreateWithFlags(&done[i], cudaEventDisableTiming);
-        if (stage_timing) for (auto &e : ev[i]) cudaEventCreate(&e);
-    }
-    auto cleanup = [&]() {
-        for (int i = 0; i < depth; i++) { cudaEventDestroy(done[i]); if (stage_timing) for (auto &e : ev[i]) cudaEventDestroy(e); }
-        cudaFreeHost(h_ring);
-    };
+    static_assert(Q_COUNT <= LJ_RING_INTS, "ring slot too small for the queue counters");
+    if ((rc = lj_ctx_ring(s->ctx)) != LJ_OK) return rc;
+    int *h_ring = s->ctx->h_ring;
+    cudaEvent_t *done = s->ctx->ring_done;
+    cudaEvent_t (*ev)[5] = s->ctx->ring_ev;
+    auto cleanup = [&]() {};
 
     cudaMemsetAsync(wp.counts, 0, 64 * sizeof(int));
     cudaMemsetAsync(wp.accum, 0, (size_t)map.K0 * map.npix_local * 3 * sizeof(double));
