@@ -269,6 +269,15 @@ int lj_image_write(lj_ctx *ctx, const char *filename, const float *rgb, int32_t 
  * checkpoint: the sums plus the sample range [sample_begin, sample_end) they cover, to be resumed with
  * lj_render_params.sample_begin / sample_end. */
 int lj_accum_finalize(lj_ctx *ctx, const double *dev_sum, int32_t width, int32_t height, int32_t spp, float *rgb_out);
+/* lj_accum_finalize without any allocation.  No counterpart in the reference: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses
+ * that forbid it).  The f32 staging image is a file-scope `static __device__` array of
+ * LJ_STATIC_FINALIZE_MAX_PIXELS * 3 floats (12 MiB, held by every GPU that loads the library until the process
+ * exits); larger images are refused with LJ_EINVAL.  It calls no cudaMalloc, cudaFree or other allocating routine; same result
+ * as lj_accum_finalize bit for bit.  All calls on a device share the array (it keeps the last call's contents; every
+ * value a call reads it writes first), so calls that overlap on the GPU race: serialise them. */
+#define LJ_STATIC_FINALIZE_MAX_PIXELS (1 << 20)
+int lj_accum_finalize_static(lj_ctx *ctx, const double *dev_sum, int32_t width, int32_t height, int32_t spp, float *rgb_out);
 int lj_accum_encode(lj_ctx *ctx, int32_t format, const double *dev_sum, int32_t width, int32_t height, int32_t spp,
                     void *out, uint64_t capacity, uint64_t *bytes);
 int lj_accum_write(lj_ctx *ctx, const char *filename, const double *dev_sum, int32_t width, int32_t height, int32_t spp);

@@ -72,7 +72,7 @@ HIT_DTYPE = np.dtype([("t", "<f4"), ("u", "<f4"), ("v", "<f4"), ("geom_id", "<i4
 ABI_SYMBOLS = ["lj_init", "lj_init_devices", "lj_ctx_device_count", "lj_shutdown", "lj_scene_create", "lj_scene_destroy", "lj_render", "lj_render_device",
                "lj_intersect_batch", "lj_scene_info", "lj_last_error", "lj_scene_desc_save", "lj_scene_desc_load",
                "lj_scene_desc_free", "lj_scene_desc_pin", "lj_image_encoded_size", "lj_image_encode", "lj_image_write",
-               "lj_accum_finalize", "lj_accum_encode", "lj_accum_write", "lj_accum_save", "lj_accum_load",
+               "lj_accum_finalize", "lj_accum_finalize_static", "lj_accum_encode", "lj_accum_write", "lj_accum_save", "lj_accum_load",
                "lj_scene_create_ex", "lj_scene_read_derived", "lj_mesh_load_obj", "lj_mesh_load_serialized",
                "lj_mesh_compute_normals", "lj_mesh_free", "lj_volume_load", "lj_volume_free"]
 
@@ -143,6 +143,7 @@ def load_library():
     lib.lj_image_encode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.lj_image_write.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32]
     lib.lj_accum_finalize.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    lib.lj_accum_finalize_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     lib.lj_accum_encode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.lj_accum_write.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
     lib.lj_accum_save.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
@@ -204,6 +205,13 @@ class LajollaGPU:
     def accum_finalize(self, dev_ptr, w, h, spp):
         out = np.empty((h, w, 3), dtype=np.float32)
         _check(self.lib, self.lib.lj_accum_finalize(self.handle, C.c_void_p(dev_ptr), w, h, int(spp), out.ctypes.data), "lj_accum_finalize")
+        return out
+
+    def accum_finalize_static(self, dev_ptr, w, h, spp, out=None):
+        """lj_accum_finalize_static: the same without any allocation (static device scratch, <= 2^20 pixels)"""
+        if out is None:
+            out = np.empty((h, w, 3), dtype=np.float32)
+        _check(self.lib, self.lib.lj_accum_finalize_static(self.handle, C.c_void_p(dev_ptr), w, h, int(spp), out.ctypes.data), "lj_accum_finalize_static")
         return out
 
     def accum_encode(self, dev_ptr, w, h, spp, fmt):

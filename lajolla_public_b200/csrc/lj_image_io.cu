@@ -11,6 +11,7 @@
 // The f64 sum -> f32 -> half conversion and the planar scanline layout are done on the device; the host
 // only writes the ~300-byte header and the line offset table.
 #include "lj_internal.h"
+#include <mutex>
 #include "lj_alloc.h"
 #include <cstdio>
 #include <cstring>
@@ -211,6 +212,52 @@ extern "C" int lj_accum_finalize(lj_ctx *ctx, const double *dev_sum, int32_t wid
     cudaError_t e = cudaMemcpy(rgb_out, dev, n * sizeof(float), cudaMemcpyDeviceToHost);
     lj_free(dev);
     if (e != cudaSuccess) { lj_set_error("lj_accum_finalize: %s", cudaGetErrorString(e)); return LJ_ECUDA; }
+    return LJ_OK;
+}
+
+// ---- allocation-free variant of lj_accum_finalize (no counterpart in the reference; see include/lajolla_gpu.h) ----
+// The f32 staging image lives in a file-scope device array instead of a cudaMallocAsync block, so the call allocates
+// nothing: usable under CUDA graph capture of the surrounding code, in serving loops and in harnesses that forbid
+// cudaMalloc.  Every GPU that loads the library holds the array (LJ_STATIC_FINALIZE_MAX_PIXELS * 3 floats = 12 MiB)
+// until the process exits.  In host code `g_finalize_scratch` is only the host-side stand-in of the symbol, never a
+// device address: the address is looked up once per device with cudaGetSymbolAddress (that device current) and the
+// kernel is given that pointer.
+static __device__ __align__(256) float g_finalize_scratch[(size_t)LJ_STATIC_FINALIZE_MAX_PIXELS * 3];
+enum { LJ_STATIC_MAX_DEVICES = 64 };
+static float *g_finalize_scratch_ptr[LJ_STATIC_MAX_DEVICES];      // per device ordinal, null until looked up
+static std::mutex g_finalize_scratch_mu;
+
+static int finalize_scratch_for(int device, float **out) {
+    if (device < 0 || device >= LJ_STATIC_MAX_DEVICES) { lj_set_error("lj_accum_finalize_static: device ordinal %d not supported (max %d)", device, LJ_STATIC_MAX_DEVICES - 1); return LJ_EUNSUPPORTED; }
+    std::lock_guard<std::mutex> lock(g_finalize_scratch_mu);
+    if (!g_finalize_scratch_ptr[device]) {
+        float *p = nullptr;
+        cudaError_t e = cudaGetSymbolAddress((void **)&p, g_finalize_scratch);     // the calling thread's current device = `device`
+        if (e != cudaSuccess || !p) { lj_set_error("lj_accum_finalize_static: cudaGetSymbolAddress failed: %s", cudaGetErrorString(e)); return LJ_ECUDA; }
+        g_finalize_scratch_ptr[device] = p;
+    }
+    *out = g_finalize_scratch_ptr[device];
+    return LJ_OK;
+}
+
+extern "C" int lj_accum_finalize_static(lj_ctx *ctx, const double *dev_sum, int32_t width, int32_t height, int32_t spp, float *rgb_out) {
+    if (!ctx || !dev_sum || !rgb_out) { lj_set_error("lj_accum_finalize_static: null argument"); return LJ_EINVAL; }
+    if (width <= 0 || height <= 0 || spp <= 0) { lj_set_error("lj_accum_finalize_static: empty image or spp <= 0"); return LJ_EINVAL; }
+    const long long npix = (long long)width * height;
+    if (npix > (long long)LJ_STATIC_FINALIZE_MAX_PIXELS) {
+        lj_set_error("lj_accum_finalize_static: %d x %d = %lld pixels exceed the static scratch of %d pixels; use lj_accum_finalize",
+                     width, height, npix, (int)LJ_STATIC_FINALIZE_MAX_PIXELS);
+        return LJ_EINVAL;
+    }
+    LJ_CUDA(cudaSetDevice(ctx->device));
+    float *dev = nullptr;
+    if (int rc = finalize_scratch_for(ctx->device, &dev)) return rc;
+    const long long n = npix * 3;
+    // every value the copy below reads is written by this launch first: nothing has to be cleared between calls
+    k_accum_to_f32<<<(unsigned)((n + 255) / 256), 256>>>(n, dev_sum, 1.0 / (double)spp, dev);
+    cudaError_t e = cudaGetLastError();
+    if (e == cudaSuccess) e = cudaMemcpy(rgb_out, dev, n * sizeof(float), cudaMemcpyDeviceToHost);
+    if (e != cudaSuccess) { lj_set_error("lj_accum_finalize_static: %s", cudaGetErrorString(e)); return LJ_ECUDA; }
     return LJ_OK;
 }
 
