@@ -52,3 +52,30 @@ def test_full_size_parity(gpu, name, key):
                 assert abs(float(img.mean()) - float(ref.mean())) <= 0.01 * abs(float(ref.mean()))
     finally:
         scene.close()
+
+
+def test_cli_drop_in_is_byte_identical_to_the_reference_binary(tmp_path):
+    """The drop-in claim itself (main.cpp:37-43): `lajolla scene.xml -o out.pfm` through the GPU library with the
+    reference's per-tile streams (LJ_RNG_MODE=A) writes the same FILE, byte for byte, as the reference's own binary
+    (oracle/_ref/lajolla_ref = unmodified main.cpp + render.cpp over the BVH shim) for cbox.xml as shipped
+    (512x512, 4 spp)."""
+    import subprocess
+    from conftest import ROOT
+    ours = os.path.join(ROOT, "lajolla_public_b200", "bin", "lajolla")
+    ref = os.path.join(ROOT, "oracle", "_ref", "lajolla_ref")
+    xml = os.path.join(ROOT, "oracle", "_ref", "scenes", "cbox", "cbox.xml")
+    if not all(os.path.exists(p) for p in (ours, ref, xml)):
+        pytest.skip("drop-in binary / reference binary / scene assets not present")
+    files = []
+    for exe, env_extra in ((ref, {}), (ours, {"LJ_RNG_MODE": "A", "LJ_DEVICE": "0"})):
+        out = tmp_path / (os.path.basename(exe) + ".pfm")
+        r = subprocess.run([exe, "-o", str(out), xml], stdout=subprocess.PIPE, stderr=subprocess.STDOUT, text=True,
+                           env=dict(os.environ, **env_extra), cwd=str(tmp_path))
+        assert r.returncode == 0, r.stdout[-2000:]
+        files.append(open(out, "rb").read())
+    assert len(files[0]) == len(files[1]) == len(b"PF\n512 512\n-1\n") + 512 * 512 * 12
+    same = files[0] == files[1]
+    if not same:
+        a = np.frombuffer(files[0][-512 * 512 * 12:], dtype="<f4"); b = np.frombuffer(files[1][-512 * 512 * 12:], dtype="<f4")
+        print(f"differing values: {(a != b).sum()} of {a.size}, max abs {np.abs(a - b).max():.3e}")
+    assert same
