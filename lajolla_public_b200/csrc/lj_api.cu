@@ -236,12 +236,38 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
     d.eps = e < 0.01 ? e : 0.01;
     d.envmap_light_id = desc->envmap_light_id;
     d.num_lights = (int)desc->num_lights; d.num_shapes = (int)desc->num_shapes; d.num_materials = (int)desc->num_materials; d.num_media = (int)desc->num_media;
+    // volume grids: f32 (one or three channels) where that is exact, see DScene::grid_f32
+    std::vector<lj_medium> dev_media(desc->media, desc->media + desc->num_media);
+    std::vector<float> grid_f32;
+    bool need_f64_grids = false;
+    if (!getenv("LJ_GRID_F64")) {
+        for (lj_medium &m : dev_media) {
+            if (m.kind != LJ_MEDIUM_HETEROGENEOUS) continue;
+            lj_volume *vols[2] = {&m.albedo, &m.density};
+            for (lj_volume *v : vols) {
+                if (v->kind != LJ_VOLUME_GRID) continue;
+                const size_t nvox = (size_t)v->resolution[0] * v->resolution[1] * v->resolution[2];
+                const double *g = desc->grid_data + v->data_offset;
+                bool exact = true, grey = true;
+                for (size_t i = 0; i < nvox * 3 && exact; i++) exact = (double)(float)g[i] == g[i];
+                for (size_t i = 0; i < nvox && grey; i++) grey = g[3 * i] == g[3 * i + 1] && g[3 * i] == g[3 * i + 2];
+                if (!exact) { need_f64_grids = true; continue; }
+                while (grid_f32.size() % 4) grid_f32.push_back(0.f);          // 16-byte aligned grids
+                v->data_offset = grid_f32.size();
+                v->_pad = grey ? 1 : 3;
+                if (grey) for (size_t i = 0; i < nvox; i++) grid_f32.push_back((float)g[3 * i]);
+                else for (size_t i = 0; i < nvox * 3; i++) grid_f32.push_back((float)g[i]);
+            }
+        }
+    } else need_f64_grids = true;
     Uploader up;
 #define UP(field, cnt) up.add(desc->field, (size_t)(cnt), &d.field);
-    UP(shapes, desc->num_shapes) UP(lights, desc->num_lights) UP(materials, desc->num_materials) UP(media, desc->num_media)
+    UP(shapes, desc->num_shapes) UP(lights, desc->num_lights) UP(materials, desc->num_materials)
+    up.add(dev_media.data(), dev_media.size(), &d.media);
+    up.add(grid_f32.data(), grid_f32.size(), &d.grid_f32);
     UP(textures, desc->num_textures) UP(images1, desc->num_images1) UP(images3, desc->num_images3)
     UP(positions, desc->num_positions * 3) UP(normals, desc->num_positions * 3) UP(uvs, desc->num_positions * 2)
-    UP(indices, desc->num_indices * 3) UP(texels, desc->num_texels) UP(tables, desc->num_tables) UP(grid_data, desc->num_grid_data)
+    UP(indices, desc->num_indices * 3) UP(texels, desc->num_texels) UP(tables, desc->num_tables) UP(grid_data, need_f64_grids ? desc->num_grid_data : 0)
 #undef UP
 
     // primitive lists for the BVH builder

@@ -371,6 +371,86 @@ __global__ void k_ploc_compact(int m, const int *valid, const int *pos, const in
     cid2[p] = cid[i]; ccount2[p] = ccount[i]; clo2[p] = clo[i]; chi2[p] = chi[i];
 }
 
+// All remaining PLOC rounds in ONE block once at most PLOC_TAIL clusters are left: the same search, merge rule
+// (mutually nearest pairs, ties keep the smaller index) and order-preserving compaction as the kernels above, with the
+// clusters in shared memory and block-wide scans instead of a launch sequence + a blocking read-back per round.  The
+// tail used to be most of the build's ~600 launches (66 k primitives: ~9 rounds get below 1024 clusters, ~60 follow).
+constexpr int PLOC_TAIL = 1024;
+__device__ __forceinline__ int block_scan_excl_1024(int v, int *warp_sums, int *total) {
+    const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
+    int x = v;
+#pragma unroll
+    for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+    if (lane == 31) warp_sums[w] = x;
+    __syncthreads();
+    if (w == 0) {
+        int s = warp_sums[lane];
+#pragma unroll
+        for (int o = 1; o < 32; o <<= 1) { int y = __shfl_up_sync(0xffffffffu, s, o); if (lane >= o) s += y; }
+        warp_sums[lane] = s;            // inclusive sums of the warp totals
+    }
+    __syncthreads();
+    const int before = w > 0 ? warp_sums[w - 1] : 0;
+    *total = warp_sums[31];
+    __syncthreads();                    // warp_sums is reused by the next call
+    return before + x - v;
+}
+__global__ void __launch_bounds__(PLOC_TAIL) k_ploc_tail(int m, int *cid, const int *ccount, const float4 *clo, const float4 *chi,
+                                                         int *left, int *right, int *count, float4 *node_lo, float4 *node_hi,
+                                                         int *node_counter, const int radius) {
+    __shared__ float4 slo[PLOC_TAIL], shi[PLOC_TAIL];
+    __shared__ int sid[PLOC_TAIL], scnt[PLOC_TAIL], snn[PLOC_TAIL], warp_sums[32];
+    const int t = threadIdx.x;
+    if (t < m) { slo[t] = clo[t]; shi[t] = chi[t]; sid[t] = cid[t]; scnt[t] = ccount[t]; }
+    int next_id = *node_counter;
+    __syncthreads();
+    while (m > 1) {
+        int bj = -1;
+        if (t < m) {
+            const float4 lo = slo[t], hi = shi[t];
+            float best = FLT_MAX;
+            const int j0 = t - radius < 0 ? 0 : t - radius, j1 = t + radius >= m ? m - 1 : t + radius;
+            for (int j = j0; j <= j1; j++) {
+                if (j == t) continue;
+                const float a = union_area(lo, hi, slo[j], shi[j]);
+                if (a < best) { best = a; bj = j; }
+            }
+            snn[t] = bj;
+        }
+        __syncthreads();
+        int keep = t < m ? 1 : 0, creates = 0;
+        float4 lo, hi; int id_l = 0, id_r = 0, c = 0;
+        if (t < m) {
+            lo = slo[t]; hi = shi[t]; id_l = sid[t]; c = scnt[t];
+            if (bj >= 0 && snn[bj] == t) {
+                if (t < bj) {
+                    creates = 1;
+                    const float4 lo2 = slo[bj], hi2 = shi[bj];
+                    lo = make_float4(fminf(lo.x, lo2.x), fminf(lo.y, lo2.y), fminf(lo.z, lo2.z), 0.f);
+                    hi = make_float4(fmaxf(hi.x, hi2.x), fmaxf(hi.y, hi2.y), fmaxf(hi.z, hi2.z), 0.f);
+                    id_r = sid[bj]; c += scnt[bj];
+                } else keep = 0;
+            }
+        }
+        int totals;
+        const int packed = block_scan_excl_1024(keep | (creates << 16), warp_sums, &totals);    // both counts stay below 2^16
+        // (the scan's barriers also order the reads above before the compacted writes below)
+        if (keep) {
+            const int p = packed & 0xffff;
+            int id = id_l;
+            if (creates) {
+                id = next_id + (packed >> 16);
+                left[id] = id_l; right[id] = id_r; count[id] = c; node_lo[id] = lo; node_hi[id] = hi;
+            }
+            slo[p] = lo; shi[p] = hi; sid[p] = id; scnt[p] = c;
+        }
+        m = totals & 0xffff;
+        next_id += totals >> 16;
+        __syncthreads();
+    }
+    if (t == 0) { cid[0] = sid[0]; *node_counter = next_id; }
+}
+
 // counts for the radix tree (LBVH path): size of the leaf range under each inner node
 __global__ void k_lbvh_counts(int n, const int *left, const int *right, int *count) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
@@ -400,7 +480,13 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
     int m = n, cur = 0, rounds = 0;
     int radius = PLOC_R;
     if (const char *e = getenv("LJ_PLOC_R")) { int v = atoi(e); if (v >= 1 && v <= PLOC_RMAX) radius = v; }
+    const bool use_tail = !getenv("LJ_PLOC_NO_TAIL");
     while (m > 1) {
+        if (use_tail && m <= PLOC_TAIL) {
+            k_ploc_tail<<<1, PLOC_TAIL>>>(m, cid[cur], cc[cur], clo[cur], chi[cur], left, right, count, node_lo, node_hi, counter, radius);
+            CK(cudaGetLastError());
+            break;
+        }
         int g = (m + PLOC_B - 1) / PLOC_B;
         k_ploc_nn<<<g, PLOC_B>>>(m, clo[cur], chi[cur], nn, radius);
         k_ploc_merge<<<(m + 255) / 256, 256>>>(m, nn, cid[cur], cc[cur], clo[cur], chi[cur], valid, left, right, count, node_lo, node_hi, counter);

@@ -43,6 +43,12 @@ struct DScene {
     const double *positions, *normals, *uvs;
     const int *indices;
     const double *texels, *tables, *grid_data;
+    // Volume grids at their native width (volume.cpp:6-104 reads f32 .vol files and widens): a grid whose values are
+    // all exactly representable as f32 is kept as f32 on the device, with one channel when the three of the Spectrum
+    // grid are equal (smoke.vol: 19.7 MB -> 3.3 MB).  Widening back in registers is exact, so lookups are
+    // bit-identical.  The DEVICE copy of lj_volume marks the storage in `_pad`: 0 = f64 x 3 in grid_data (fallback),
+    // 1 / 3 = f32 with that many channels in grid_f32; data_offset then counts floats.
+    const float *grid_f32;
     const double *light_pmf, *light_cdf;
 
     // ray casting structures (f32, the Embree seam of intersection.cpp:15-24)

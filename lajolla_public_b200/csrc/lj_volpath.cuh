@@ -20,6 +20,18 @@
 #include "lj_path.cuh"
 
 LJ_D d3 exp3(d3 a) { return mk3(exp(a.x), exp(a.y), exp(a.z)); }   // spectrum.h:28-30
+LJ_D d3 load3f(const float *p, size_t i) { return mk3((double)__ldg(p + 3 * i), (double)__ldg(p + 3 * i + 1), (double)__ldg(p + 3 * i + 2)); }
+// volume.h:68-80: the trilinear blend, terms added in the reference's order
+LJ_D d3 volume_blend(double scale, double dx, double dy, double dz, d3 v000, d3 v001, d3 v010, d3 v011, d3 v100, d3 v101, d3 v110, d3 v111) {
+    return scale * (v000 * ((1 - dx) * (1 - dy) * (1 - dz)) +
+                    v001 * (dx * (1 - dy) * (1 - dz)) +
+                    v010 * ((1 - dx) * dy * (1 - dz)) +
+                    v011 * (dx * dy * (1 - dz)) +
+                    v100 * ((1 - dx) * (1 - dy) * dz) +
+                    v101 * (dx * (1 - dy) * dz) +
+                    v110 * ((1 - dx) * dy * dz) +
+                    v111 * (dx * dy * dz));
+}
 
 // ---- volume.h:45-81: trilinear lookup in double, zero outside the grid's box ----
 LJ_D d3 volume_lookup(const DScene &sc, const lj_volume &v, d3 p) {
@@ -32,21 +44,38 @@ LJ_D d3 volume_lookup(const DScene &sc, const lj_volume &v, d3 p) {
     int x0 = clampi((int)pn.x, 0, rx - 1), y0 = clampi((int)pn.y, 0, ry - 1), z0 = clampi((int)pn.z, 0, rz - 1);
     int x1 = clampi(x0 + 1, 0, rx - 1), y1 = clampi(y0 + 1, 0, ry - 1), z1 = clampi(z0 + 1, 0, rz - 1);
     double dx = pn.x - x0, dy = pn.y - y0, dz = pn.z - z0;
-    const double *g = sc.grid_data + v.data_offset;
-    d3 v000 = load3(g, (size_t)(z0 * ry + y0) * rx + x0), v001 = load3(g, (size_t)(z0 * ry + y0) * rx + x1);
-    d3 v010 = load3(g, (size_t)(z0 * ry + y1) * rx + x0), v011 = load3(g, (size_t)(z0 * ry + y1) * rx + x1);
-    d3 v100 = load3(g, (size_t)(z1 * ry + y0) * rx + x0), v101 = load3(g, (size_t)(z1 * ry + y0) * rx + x1);
-    d3 v110 = load3(g, (size_t)(z1 * ry + y1) * rx + x0), v111 = load3(g, (size_t)(z1 * ry + y1) * rx + x1);
-    return v.scale * (v000 * ((1 - dx) * (1 - dy) * (1 - dz)) +
-                      v001 * (dx * (1 - dy) * (1 - dz)) +
-                      v010 * ((1 - dx) * dy * (1 - dz)) +
-                      v011 * (dx * dy * (1 - dz)) +
-                      v100 * ((1 - dx) * (1 - dy) * dz) +
-                      v101 * (dx * (1 - dy) * dz) +
-                      v110 * ((1 - dx) * dy * dz) +
-                      v111 * (dx * dy * dz));
+    const size_t i000 = (size_t)(z0 * ry + y0) * rx + x0, i001 = (size_t)(z0 * ry + y0) * rx + x1;
+    const size_t i010 = (size_t)(z0 * ry + y1) * rx + x0, i011 = (size_t)(z0 * ry + y1) * rx + x1;
+    const size_t i100 = (size_t)(z1 * ry + y0) * rx + x0, i101 = (size_t)(z1 * ry + y0) * rx + x1;
+    const size_t i110 = (size_t)(z1 * ry + y1) * rx + x0, i111 = (size_t)(z1 * ry + y1) * rx + x1;
+    if (v._pad == 1) {
+        // one f32 channel (the three channels of the Spectrum grid are equal): the same expression once; every
+        // channel of the reference's result is this value
+        const float *gf = sc.grid_f32 + v.data_offset;
+        const double a000 = (double)__ldg(gf + i000), a001 = (double)__ldg(gf + i001), a010 = (double)__ldg(gf + i010), a011 = (double)__ldg(gf + i011);
+        const double a100 = (double)__ldg(gf + i100), a101 = (double)__ldg(gf + i101), a110 = (double)__ldg(gf + i110), a111 = (double)__ldg(gf + i111);
+        const double r = v.scale * (a000 * ((1 - dx) * (1 - dy) * (1 - dz)) +
+                                    a001 * (dx * (1 - dy) * (1 - dz)) +
+                                    a010 * ((1 - dx) * dy * (1 - dz)) +
+                                    a011 * (dx * dy * (1 - dz)) +
+                                    a100 * ((1 - dx) * (1 - dy) * dz) +
+                                    a101 * (dx * (1 - dy) * dz) +
+                                    a110 * ((1 - dx) * dy * dz) +
+                                    a111 * (dx * dy * dz));
+        return mk3(r);
+    }
+    d3 v000, v001, v010, v011, v100, v101, v110, v111;
+    if (v._pad == 3) {
+        const float *gf = sc.grid_f32 + v.data_offset;
+        v000 = load3f(gf, i000); v001 = load3f(gf, i001); v010 = load3f(gf, i010); v011 = load3f(gf, i011);
+        v100 = load3f(gf, i100); v101 = load3f(gf, i101); v110 = load3f(gf, i110); v111 = load3f(gf, i111);
+    } else {
+        const double *g = sc.grid_data + v.data_offset;
+        v000 = load3(g, i000); v001 = load3(g, i001); v010 = load3(g, i010); v011 = load3(g, i011);
+        v100 = load3(g, i100); v101 = load3(g, i101); v110 = load3(g, i110); v111 = load3(g, i111);
+    }
+    return volume_blend(v.scale, dx, dy, dz, v000, v001, v010, v011, v100, v101, v110, v111);
 }
-
 // volume.h:122-141 (pbrt slab test from t=0 to ray.tfar; tnear is ignored as in the reference)
 LJ_D bool volume_intersect(const lj_volume &v, const Ray &ray) {
     if (v.kind == LJ_VOLUME_CONSTANT) return true;
