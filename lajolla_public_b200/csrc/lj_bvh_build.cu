@@ -18,6 +18,20 @@
 
 #define CK(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { snprintf(err, 256, "%s: %s", #x, cudaGetErrorString(e_)); return -1; } } while (0)
 
+// LJ_BVH_TRACE=1: host wall-clock per build phase (each boundary synchronises, so only for diagnosis)
+#include <chrono>
+struct BvhPhaseTimer {
+    bool on; std::chrono::steady_clock::time_point t0;
+    BvhPhaseTimer() : on(getenv("LJ_BVH_TRACE") != nullptr) { if (on) { cudaStreamSynchronize(0); t0 = std::chrono::steady_clock::now(); } }
+    void mark(const char *what) {
+        if (!on) return;
+        cudaStreamSynchronize(0);
+        auto t1 = std::chrono::steady_clock::now();
+        fprintf(stderr, "[bvh] %-28s %8.3f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
+
 namespace {
 
 __device__ __forceinline__ void atomic_min_f(float *addr, float v) {
@@ -320,8 +334,12 @@ __global__ void k_ploc_init(int n, const int *vals, const float4 *prim_lo, const
     cid[i] = ~i; ccount[i] = 1; clo[i] = prim_lo[p]; chi[i] = prim_hi[p];
 }
 
-__global__ void __launch_bounds__(PLOC_B) k_ploc_nn(int m, const float4 *clo, const float4 *chi, int *nn, const int PLOC_R) {
+// The cluster count `m` of a round lives on the device (*m_ptr): the host sizes grids from the last count it read
+// (an upper bound, counts only fall) and reads the count back every few rounds instead of after each one.
+__global__ void __launch_bounds__(PLOC_B) k_ploc_nn(const int *m_ptr, const float4 *clo, const float4 *chi, int *nn, const int PLOC_R) {
     __shared__ float4 slo[PLOC_B + 2 * PLOC_RMAX], shi[PLOC_B + 2 * PLOC_RMAX];
+    const int m = *m_ptr;
+    if (blockIdx.x * PLOC_B >= m) return;
     int base = blockIdx.x * PLOC_B - PLOC_R;
     for (int t = threadIdx.x; t < PLOC_B + 2 * PLOC_R; t += PLOC_B) {
         int g = base + t;
@@ -342,10 +360,11 @@ __global__ void __launch_bounds__(PLOC_B) k_ploc_nn(int m, const float4 *clo, co
     nn[i] = bj;
 }
 
-__global__ void k_ploc_merge(int m, const int *nn, int *cid, int *ccount, float4 *clo, float4 *chi, int *valid,
+__global__ void k_ploc_merge(const int *m_ptr, int m_upper, const int *nn, int *cid, int *ccount, float4 *clo, float4 *chi, int *valid,
                              int *left, int *right, int *count, float4 *node_lo, float4 *node_hi, int *node_counter) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
-    if (i >= m) return;
+    const int m = *m_ptr;
+    if (i >= m) { if (i <= m_upper) valid[i] = 0; return; }      // the scan runs over m_upper + 1 flags
     int j = nn[i];
     int v = 1;
     if (j >= 0 && nn[j] == i) {
@@ -363,9 +382,11 @@ __global__ void k_ploc_merge(int m, const int *nn, int *cid, int *ccount, float4
     valid[i] = v;
 }
 
-__global__ void k_ploc_compact(int m, const int *valid, const int *pos, const int *cid, const int *ccount,
+__global__ void k_ploc_compact(const int *m_ptr, int m_upper, int *m_next, const int *valid, const int *pos, const int *cid, const int *ccount,
                                const float4 *clo, const float4 *chi, int *cid2, int *ccount2, float4 *clo2, float4 *chi2) {
     int i = blockIdx.x * blockDim.x + threadIdx.x;
+    const int m = *m_ptr;
+    if (i == 0) *m_next = pos[m_upper];       // clusters left after this round
     if (i >= m || !valid[i]) return;
     int p = pos[i];
     cid2[p] = cid[i]; ccount2[p] = ccount[i]; clo2[p] = clo[i]; chi2[p] = chi[i];
@@ -395,12 +416,13 @@ __device__ __forceinline__ int block_scan_excl_1024(int v, int *warp_sums, int *
     __syncthreads();                    // warp_sums is reused by the next call
     return before + x - v;
 }
-__global__ void __launch_bounds__(PLOC_TAIL) k_ploc_tail(int m, int *cid, const int *ccount, const float4 *clo, const float4 *chi,
+__global__ void __launch_bounds__(PLOC_TAIL) k_ploc_tail(const int *m_ptr, int *cid, const int *ccount, const float4 *clo, const float4 *chi,
                                                          int *left, int *right, int *count, float4 *node_lo, float4 *node_hi,
                                                          int *node_counter, const int radius) {
     __shared__ float4 slo[PLOC_TAIL], shi[PLOC_TAIL];
     __shared__ int sid[PLOC_TAIL], scnt[PLOC_TAIL], snn[PLOC_TAIL], warp_sums[32];
     const int t = threadIdx.x;
+    int m = *m_ptr;
     if (t < m) { slo[t] = clo[t]; shi[t] = chi[t]; sid[t] = cid[t]; scnt[t] = ccount[t]; }
     int next_id = *node_counter;
     __syncthreads();
@@ -473,31 +495,44 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
         CK(lj_malloc(&clo[b], sizeof(float4) * n)); CK(lj_malloc(&chi[b], sizeof(float4) * n));
     }
     CK(lj_malloc(&nn, 4 * (size_t)n)); CK(lj_malloc(&valid, 4 * (size_t)(n + 1))); CK(lj_malloc(&pos, 4 * (size_t)(n + 1)));
-    CK(lj_malloc(&counter, 4)); CK(cudaMemset(counter, 0, 4));
+    CK(lj_malloc(&counter, 3 * 4));             // [0] next node id, [1], [2] cluster count before / after a round (alternating)
+    {
+        const int init[3] = {0, n, n};
+        CK(cudaMemcpy(counter, init, sizeof init, cudaMemcpyHostToDevice));
+    }
     CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, valid, pos, n + 1));
     CK(lj_malloc(&tmp, tmp_bytes));
     k_ploc_init<<<(n + 255) / 256, 256>>>(n, vals, prim_lo, prim_hi, cid[0], cc[0], clo[0], chi[0]);
-    int m = n, cur = 0, rounds = 0;
+    int m = n, cur = 0, rounds = 0;     // m: the last count the host has seen
     int radius = PLOC_R;
     if (const char *e = getenv("LJ_PLOC_R")) { int v = atoi(e); if (v >= 1 && v <= PLOC_RMAX) radius = v; }
     const bool use_tail = !getenv("LJ_PLOC_NO_TAIL");
+    const bool trace = getenv("LJ_BVH_TRACE") != nullptr;
+    int batch = 4;                      // rounds between two read-backs of the cluster count
+    if (const char *e = getenv("LJ_PLOC_BATCH")) { int v = atoi(e); if (v >= 1 && v <= 64) batch = v; }
     while (m > 1) {
+        int *m_in = counter + 1 + (rounds & 1);
         if (use_tail && m <= PLOC_TAIL) {
-            k_ploc_tail<<<1, PLOC_TAIL>>>(m, cid[cur], cc[cur], clo[cur], chi[cur], left, right, count, node_lo, node_hi, counter, radius);
+            k_ploc_tail<<<1, PLOC_TAIL>>>(m_in, cid[cur], cc[cur], clo[cur], chi[cur], left, right, count, node_lo, node_hi, counter, radius);
             CK(cudaGetLastError());
             break;
         }
-        int g = (m + PLOC_B - 1) / PLOC_B;
-        k_ploc_nn<<<g, PLOC_B>>>(m, clo[cur], chi[cur], nn, radius);
-        k_ploc_merge<<<(m + 255) / 256, 256>>>(m, nn, cid[cur], cc[cur], clo[cur], chi[cur], valid, left, right, count, node_lo, node_hi, counter);
-        CK(cudaMemsetAsync(valid + m, 0, 4));
-        CK(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, valid, pos, m + 1));
-        k_ploc_compact<<<(m + 255) / 256, 256>>>(m, valid, pos, cid[cur], cc[cur], clo[cur], chi[cur], cid[1 - cur], cc[1 - cur], clo[1 - cur], chi[1 - cur]);
+        const int m_upper = m;
+        for (int b = 0; b < batch; b++) {
+            m_in = counter + 1 + (rounds & 1);
+            int *m_out = counter + 1 + ((rounds + 1) & 1);
+            k_ploc_nn<<<(m_upper + PLOC_B - 1) / PLOC_B, PLOC_B>>>(m_in, clo[cur], chi[cur], nn, radius);
+            k_ploc_merge<<<(m_upper + 1 + 255) / 256, 256>>>(m_in, m_upper, nn, cid[cur], cc[cur], clo[cur], chi[cur], valid, left, right, count, node_lo, node_hi, counter);
+            CK(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, valid, pos, m_upper + 1));
+            k_ploc_compact<<<(m_upper + 255) / 256, 256>>>(m_in, m_upper, m_out, valid, pos, cid[cur], cc[cur], clo[cur], chi[cur], cid[1 - cur], cc[1 - cur], clo[1 - cur], chi[1 - cur]);
+            cur = 1 - cur;
+            if (++rounds > 4096) { snprintf(err, 256, "PLOC did not converge"); return -1; }
+        }
         int m_new = 0;
-        CK(cudaMemcpy(&m_new, pos + m, 4, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&m_new, counter + 1 + (rounds & 1), 4, cudaMemcpyDeviceToHost));
         if (m_new >= m || m_new < 1) { snprintf(err, 256, "PLOC made no progress (%d -> %d clusters)", m, m_new); return -1; }
-        m = m_new; cur = 1 - cur;
-        if (++rounds > 4096) { snprintf(err, 256, "PLOC did not converge"); return -1; }
+        if (trace) fprintf(stderr, "[bvh]   PLOC after round %d: %d -> %d clusters\n", rounds, m, m_new);
+        m = m_new;
     }
     CK(cudaMemcpy(root_out, cid[cur], 4, cudaMemcpyDeviceToHost));
     for (int b = 0; b < 2; b++) { lj_free(cid[b]); lj_free(cc[b]); lj_free(clo[b]); lj_free(chi[b]); }
@@ -515,6 +550,7 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
     if (n == 0) return 0;
     const int B = 256;
     const int G = (n + B - 1) / B;
+    BvhPhaseTimer pt;
     float4 *prim_lo = nullptr, *prim_hi = nullptr;
     float *bounds = nullptr;
     CK(lj_malloc(&prim_lo, sizeof(float4) * n)); CK(lj_malloc(&prim_hi, sizeof(float4) * n));
@@ -525,6 +561,7 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
     CK(cudaGetLastError());
     CK(cudaMemcpy(out.lo, bounds, sizeof(float) * 3, cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(out.hi, bounds + 3, sizeof(float) * 3, cudaMemcpyDeviceToHost));
+    pt.mark("primitive bounds");
 
     // ---- triangle pre-splitting: primitives -> references (see k_split_refs) ----
     const int n_prims_in = n;
@@ -576,6 +613,7 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     const int B = 256;
     const int G = (n + B - 1) / B;
     out.num_prims = n;
+    BvhPhaseTimer pt;
     float4 *node_lo = nullptr, *node_hi = nullptr;
     unsigned long long *keys = nullptr, *keys2 = nullptr;
     int *vals = nullptr, *vals2 = nullptr, *left = nullptr, *right = nullptr, *par_i = nullptr, *par_l = nullptr, *flags = nullptr, *count = nullptr;
@@ -588,10 +626,12 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
     CK(lj_malloc(&tmp, tmp_bytes));
     CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
+    pt.mark("morton + radix sort");
 
     CK(lj_malloc(&out.tri_verts, sizeof(float4) * 3 * (size_t)n));
     k_emit_prims<<<G, B>>>(n, in.num_tris, vals2, ref_prim, in.positions, in.indices, in.tri_shape, in.shapes, in.spheres, out.tri_verts);
     CK(cudaGetLastError());
+    pt.mark("emit primitives");
 
     if (n >= 2) {
         CK(lj_malloc(&left, 4 * (size_t)n)); CK(lj_malloc(&right, 4 * (size_t)n));
@@ -610,14 +650,17 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
         } else {
             if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, &out.bvh2_root, err) != 0) return -1;
         }
+        pt.mark("PLOC");
         CK(lj_malloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
         k_emit_bvh2<<<G, B>>>(n, left, right, node_lo, node_hi, out.bvh2);
         CK(cudaGetLastError());
         out.num_bvh2 = n - 1;
     }
-    CK(cudaDeviceSynchronize());
+    CK(cudaStreamSynchronize(0));
+    pt.mark("emit binary tree");
     // the 8-wide collapse consumes the binary tree (lj_bvh8_build.cu)
     int rc = lj_bvh8_collapse(n, out.bvh2_root, out.tri_verts, left, right, count, node_lo, node_hi, vals2, prim_lo, prim_hi, out, err);
+    pt.mark("8-wide collapse");
     lj_free(ref_prim);
     lj_free(prim_lo); lj_free(prim_hi); lj_free(bounds); lj_free(keys); lj_free(keys2); lj_free(vals); lj_free(vals2);
     lj_free(left); lj_free(right); lj_free(par_i); lj_free(par_l); lj_free(flags); lj_free(node_lo); lj_free(node_hi); lj_free(tmp); lj_free(count);
