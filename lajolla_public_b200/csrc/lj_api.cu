@@ -298,6 +298,11 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
         cudaEventRecord(e1);
     }
 
+    if ((rc = lj_scene_build_shading_cache(s, desc, d_tri_shape)) != LJ_OK) {
+        cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc;
+    }
+    cudaEventRecord(e1);
+
     BvhBuildInput bi;
     bi.num_tris = (int)desc->num_indices; bi.num_spheres = (int)spheres.size();
     bi.positions = d.positions; bi.indices = d.indices; bi.tri_shape = d_tri_shape; bi.shapes = d.shapes; bi.spheres = d_spheres;

@@ -67,5 +67,7 @@ int lj_render_volpath(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
 int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_stats *st);
 // scene.cpp:36-52 on the device (lj_scene_build.cu)
 int lj_scene_build_tables(lj_scene *s, const lj_scene_desc *desc, bool poison, float *elapsed_ms);
+// per-triangle shading records + f32 level-0 texels (DScene::tri_shade, texels0_*), lj_scene_build.cu
+int lj_scene_build_shading_cache(lj_scene *s, const lj_scene_desc *desc, const int *d_tri_shape);
 
 #define LJ_CUDA(x) do { cudaError_t e_ = (x); if (e_ != cudaSuccess) { lj_set_error("%s failed: %s (%s:%d)", #x, cudaGetErrorString(e_), __FILE__, __LINE__); return LJ_ECUDA; } } while (0)

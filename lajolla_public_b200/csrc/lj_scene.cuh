@@ -51,6 +51,20 @@ struct DScene {
     const float *grid_f32;
     const double *light_pmf, *light_cdf;
 
+    // Shading caches derived on the device at scene creation (lj_scene_build.cu, lj_scene_build_shading_cache):
+    //  * tri_shade: one 192-byte record per triangle (global triangle index = lj_shape.triangle_offset + primID):
+    //    the f64 positions, normals and uvs of its three vertices, contiguous and 64-byte aligned -- one dependent
+    //    fetch of six aligned sectors where the indexed layout needs the index triple first and then nine
+    //    unaligned 16/24-byte gathers;
+    //  * level 0 of every mip chain whose texels are exactly representable as f32 (image.cpp:94-108 widens
+    //    stbi_loadf floats, so they are) as float4 (RGB) / float (scalar): tex0_off*[image] is the image's first
+    //    texel in texels0_*, or 0xffffffff when the image keeps its f64 level 0.  Bounce rays carry a zero ray
+    //    differential (intersection.h:41), so all but the camera-ray lookups read level 0.
+    // Widening back to f64 in registers is exact: shading is bit-identical with and without the caches.
+    const double *tri_shade;
+    const float4 *texels0_rgb; const float *texels0_r;
+    const unsigned *tex0_off3, *tex0_off1;
+
     // ray casting structures (f32, the Embree seam of intersection.cpp:15-24)
     int num_tris, num_spheres, num_prims;
     const float4 *tri_verts;    // 3 float4 per primitive slot in BVH leaf order: (v0, geom) (v1, prim) (v2, kind)

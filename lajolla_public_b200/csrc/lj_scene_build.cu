@@ -108,7 +108,7 @@ __global__ void k_env_f(DScene sc, lj_image img, int w, int h, double *f) {
     const double v = (y + 0.5) / (double)h;
     const double sin_elevation = sin(LJ_PI * v);
     const double u = (x + 0.5) / (double)w;
-    f[i] = luminance(mip_lookup_level<d3>(sc, img, u, v, 0)) * sin_elevation;
+    f[i] = luminance(mip_lookup_level<d3>(sc, img, -1, u, v, 0)) * sin_elevation;   // (the f32 level-0 cache is built later)
 }
 
 // rows of make_table_dist_2d (table_dist.cpp:44-73): one block per row; pdf_rows holds f on entry
@@ -251,5 +251,108 @@ int lj_scene_build_tables(lj_scene *s, const lj_scene_desc *desc, bool poison, f
     LJ_CUDA(cudaEventSynchronize(e1));
     if (elapsed_ms) cudaEventElapsedTime(elapsed_ms, e0, e1);
     cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return LJ_OK;
+}
+
+// ---------------- shading caches (DScene::tri_shade, texels0_*) ----------------
+namespace {
+
+// one 192-byte record per triangle: p0 p1 p2 | n0 n1 n2 | uv0 uv1 uv2 (f64; zeros where the mesh has no normals / uvs)
+__global__ void k_tri_shade(int num_tris, const int *tri_shape, const lj_shape *shapes, const int *indices,
+                            const double *positions, const double *normals, const double *uvs, double *out) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= num_tris) return;
+    const lj_shape &s = shapes[tri_shape[i]];
+    double *o = out + 24 * (size_t)i;
+    for (int k = 0; k < 3; k++) {
+        const size_t v = (size_t)s.vertex_offset + indices[3 * (size_t)i + k];
+        for (int a = 0; a < 3; a++) {
+            o[3 * k + a] = positions[3 * v + a];
+            o[9 + 3 * k + a] = s.has_normals ? normals[3 * v + a] : 0.0;
+        }
+        for (int a = 0; a < 2; a++) o[18 + 2 * k + a] = s.has_uvs ? uvs[2 * v + a] : 0.0;
+    }
+}
+
+struct Tex0Image { unsigned long long src; unsigned start, count; };    // level-0 texels in `texels` (doubles), first texel / texel count in the f32 array
+
+// image of the t-th level-0 texel (images are few: linear search over the prefix table)
+__device__ __forceinline__ int tex0_image_of(const Tex0Image *imgs, int n, unsigned t) {
+    int i = 0;
+    while (i + 1 < n && t >= imgs[i + 1].start) i++;
+    return i;
+}
+template <int C>
+__global__ void k_tex0_check(const Tex0Image *imgs, int n, unsigned total, const double *texels, int *inexact) {
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const int i = tex0_image_of(imgs, n, t);
+        const double *p = texels + imgs[i].src + (size_t)C * (t - imgs[i].start);
+        bool ok = true;
+        for (int c = 0; c < C; c++) ok = ok && (double)(float)p[c] == p[c];
+        if (!ok) inexact[i] = 1;
+    }
+}
+template <int C>
+__global__ void k_tex0_convert(const Tex0Image *imgs, int n, unsigned total, const double *texels, float4 *rgb, float *r) {
+    for (unsigned t = blockIdx.x * blockDim.x + threadIdx.x; t < total; t += gridDim.x * blockDim.x) {
+        const int i = tex0_image_of(imgs, n, t);
+        const double *p = texels + imgs[i].src + (size_t)C * (t - imgs[i].start);
+        if (C == 3) rgb[t] = make_float4((float)p[0], (float)p[1], (float)p[2], 0.f);
+        else r[t] = (float)p[0];
+    }
+}
+__global__ void k_tex0_offsets(const Tex0Image *imgs, int n, const int *inexact, unsigned *off) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) off[i] = inexact[i] ? 0xffffffffu : imgs[i].start;
+}
+
+}  // namespace
+
+// Builds DScene::tri_shade and the f32 level-0 texel arrays; everything stays on the device (the exactness of an image
+// is decided by a kernel and lands in tex0_off*, the host never waits).  LJ_NO_SHADE_CACHE=1 skips both (A/B runs).
+int lj_scene_build_shading_cache(lj_scene *s, const lj_scene_desc *desc, const int *d_tri_shape) {
+    DScene &d = s->d;
+    d.tri_shade = nullptr; d.texels0_rgb = nullptr; d.texels0_r = nullptr; d.tex0_off3 = nullptr; d.tex0_off1 = nullptr;
+    if (getenv("LJ_NO_SHADE_CACHE")) return LJ_OK;
+    const int nt = (int)desc->num_indices;
+    if (nt > 0) {
+        double *ts = nullptr;
+        LJ_CUDA(lj_malloc(&ts, sizeof(double) * 24 * (size_t)nt));
+        s->allocs.push_back(ts);
+        k_tri_shade<<<(nt + 127) / 128, 128>>>(nt, d_tri_shape, d.shapes, d.indices, d.positions, d.normals, d.uvs, ts);
+        LJ_CUDA(cudaGetLastError());
+        d.tri_shade = ts;
+    }
+    for (int c = 0; c < 2; c++) {
+        const lj_image *imgs = c ? desc->images3 : desc->images1;
+        const int ni = (int)(c ? desc->num_images3 : desc->num_images1);
+        if (ni == 0) continue;
+        std::vector<Tex0Image> tab(ni);
+        unsigned long long total = 0;
+        for (int i = 0; i < ni; i++) {
+            tab[i].src = imgs[i].offset[0]; tab[i].start = (unsigned)total; tab[i].count = (unsigned)((size_t)imgs[i].width[0] * imgs[i].height[0]);
+            total += tab[i].count;
+        }
+        if (total == 0 || total >= 0xffffffffull) continue;
+        Tex0Image *d_tab = nullptr; int *d_inexact = nullptr; unsigned *d_off = nullptr; void *d_tex = nullptr;
+        LJ_CUDA(lj_malloc(&d_tab, sizeof(Tex0Image) * ni)); s->allocs.push_back(d_tab);
+        LJ_CUDA(lj_malloc(&d_inexact, sizeof(int) * ni)); s->allocs.push_back(d_inexact);
+        LJ_CUDA(lj_malloc(&d_off, sizeof(unsigned) * ni)); s->allocs.push_back(d_off);
+        LJ_CUDA(lj_malloc(&d_tex, (c ? sizeof(float4) : sizeof(float)) * (size_t)total)); s->allocs.push_back(d_tex);
+        LJ_CUDA(cudaMemcpyAsync(d_tab, tab.data(), sizeof(Tex0Image) * ni, cudaMemcpyHostToDevice));
+        LJ_CUDA(cudaMemsetAsync(d_inexact, 0, sizeof(int) * ni));
+        const unsigned grid = (unsigned)std::min<unsigned long long>((total + 255) / 256, (unsigned long long)s->ctx->sm_count * 16);
+        if (c) {
+            k_tex0_check<3><<<grid, 256>>>(d_tab, ni, (unsigned)total, d.texels, d_inexact);
+            k_tex0_convert<3><<<grid, 256>>>(d_tab, ni, (unsigned)total, d.texels, (float4 *)d_tex, nullptr);
+        } else {
+            k_tex0_check<1><<<grid, 256>>>(d_tab, ni, (unsigned)total, d.texels, d_inexact);
+            k_tex0_convert<1><<<grid, 256>>>(d_tab, ni, (unsigned)total, d.texels, nullptr, (float *)d_tex);
+        }
+        k_tex0_offsets<<<(ni + 63) / 64, 64>>>(d_tab, ni, d_inexact, d_off);
+        LJ_CUDA(cudaGetLastError());
+        if (c) { d.texels0_rgb = (const float4 *)d_tex; d.tex0_off3 = d_off; }
+        else { d.texels0_r = (const float *)d_tex; d.tex0_off1 = d_off; }
+    }
     return LJ_OK;
 }

@@ -12,11 +12,18 @@ template <> struct Texel<3> { typedef d3 T; };
 LJ_D double texel_load(const double *p, size_t i, double *) { return __ldg(p + i); }
 LJ_D d3 texel_load(const double *p, size_t i, d3 *) { return mk3(__ldg(p + 3 * i), __ldg(p + 3 * i + 1), __ldg(p + 3 * i + 2)); }
 
+// level-0 texels kept as f32 (DScene::texels0_*): same values, widened
+LJ_D unsigned tex0_offset(const DScene &sc, int image_id, double *) { return sc.tex0_off1 ? __ldg(sc.tex0_off1 + image_id) : 0xffffffffu; }
+LJ_D unsigned tex0_offset(const DScene &sc, int image_id, d3 *) { return sc.tex0_off3 ? __ldg(sc.tex0_off3 + image_id) : 0xffffffffu; }
+LJ_D double texel0_load(const DScene &sc, size_t i, double *) { return (double)__ldg(sc.texels0_r + i); }
+LJ_D d3 texel0_load(const DScene &sc, size_t i, d3 *) { const float4 t = __ldg(sc.texels0_rgb + i); return mk3((double)t.x, (double)t.y, (double)t.z); }
+
 // mipmap.h:50-69 lookup at an integer level
 template <typename T>
-LJ_D T mip_lookup_level(const DScene &sc, const lj_image &img, double u, double v, int level) {
+LJ_D T mip_lookup_level(const DScene &sc, const lj_image &img, int image_id, double u, double v, int level) {
     int W = img.width[level], H = img.height[level];
     const double *base = sc.texels + img.offset[level];
+    const unsigned off0 = level == 0 ? tex0_offset(sc, image_id, (T *)nullptr) : 0xffffffffu;
     u = u * W - 0.5;
     v = v * H - 0.5;
     int ufi = modulo_i((int)u, W);
@@ -25,10 +32,18 @@ LJ_D T mip_lookup_level(const DScene &sc, const lj_image &img, double u, double 
     int vci = modulo_i(vfi + 1, H);
     double u_off = u - ufi;
     double v_off = v - vfi;
-    T ff = texel_load(base, (size_t)vfi * W + ufi, (T *)nullptr);
-    T fc = texel_load(base, (size_t)vci * W + ufi, (T *)nullptr);
-    T cf = texel_load(base, (size_t)vfi * W + uci, (T *)nullptr);
-    T cc = texel_load(base, (size_t)vci * W + uci, (T *)nullptr);
+    T ff, fc, cf, cc;
+    if (off0 != 0xffffffffu) {
+        ff = texel0_load(sc, off0 + (size_t)vfi * W + ufi, (T *)nullptr);
+        fc = texel0_load(sc, off0 + (size_t)vci * W + ufi, (T *)nullptr);
+        cf = texel0_load(sc, off0 + (size_t)vfi * W + uci, (T *)nullptr);
+        cc = texel0_load(sc, off0 + (size_t)vci * W + uci, (T *)nullptr);
+    } else {
+        ff = texel_load(base, (size_t)vfi * W + ufi, (T *)nullptr);
+        fc = texel_load(base, (size_t)vci * W + ufi, (T *)nullptr);
+        cf = texel_load(base, (size_t)vfi * W + uci, (T *)nullptr);
+        cc = texel_load(base, (size_t)vci * W + uci, (T *)nullptr);
+    }
     return ff * (1 - u_off) * (1 - v_off) +
            fc * (1 - u_off) * v_off +
            cf * u_off * (1 - v_off) +
@@ -37,18 +52,18 @@ LJ_D T mip_lookup_level(const DScene &sc, const lj_image &img, double u, double 
 
 // mipmap.h:71-88 trilinear lookup at a real level
 template <typename T>
-LJ_D T mip_lookup(const DScene &sc, const lj_image &img, double u, double v, double level) {
+LJ_D T mip_lookup(const DScene &sc, const lj_image &img, int image_id, double u, double v, double level) {
     int n = img.num_levels;
     if (level <= 0) {
-        return mip_lookup_level<T>(sc, img, u, v, 0);
+        return mip_lookup_level<T>(sc, img, image_id, u, v, 0);
     } else if (level < (double)(n - 1)) {
         int flevel = clampi((int)floor(level), 0, n - 1);
         int clevel = clampi(flevel + 1, 0, n - 1);
         double level_off = level - flevel;
-        return mip_lookup_level<T>(sc, img, u, v, flevel) * (1 - level_off) +
-               mip_lookup_level<T>(sc, img, u, v, clevel) * level_off;
+        return mip_lookup_level<T>(sc, img, image_id, u, v, flevel) * (1 - level_off) +
+               mip_lookup_level<T>(sc, img, image_id, u, v, clevel) * level_off;
     } else {
-        return mip_lookup_level<T>(sc, img, u, v, n - 1);
+        return mip_lookup_level<T>(sc, img, image_id, u, v, n - 1);
     }
 }
 
@@ -68,7 +83,7 @@ LJ_D T eval_texture_t(const DScene &sc, int tex_id, d2 uv, double footprint) {
         int wh = img.width[0] > img.height[0] ? img.width[0] : img.height[0];
         double scaled_footprint = wh * lmax(t.uscale, t.vscale) * footprint;
         double level = log2(lmax(scaled_footprint, (double)1e-8f));
-        return mip_lookup<T>(sc, img, lu, lv, level);
+        return mip_lookup<T>(sc, img, t.image_id, lu, lv, level);
     } else {
         double lu = modulo_one(uv.x * t.uscale + t.uoffset);
         double lv = modulo_one(uv.y * t.vscale + t.voffset);
@@ -105,18 +120,44 @@ LJ_D d2 load2(const double *p, size_t i) { return mk2(__ldg(p + 2 * i), __ldg(p 
 struct ShadingInfo { d2 uv; Frame shading_frame; double mean_curvature, inv_uv_size; };
 
 // shapes/triangle_mesh.inl:65-157
+// the three vertices of a triangle: from its 192-byte record (DScene::tri_shade: twelve aligned 16-byte loads, issued
+// together) or, without the cache, through the index triple
+struct TriVerts { d3 p0, p1, p2, n0, n1, n2; d2 uv0, uv1, uv2; };
+LJ_D TriVerts load_tri_verts(const DScene &sc, const lj_shape &s, int prim, bool want_normals, bool want_uvs) {
+    TriVerts t;
+    if (sc.tri_shade) {
+        const double2 *r = reinterpret_cast<const double2 *>(sc.tri_shade + 24 * ((size_t)s.triangle_offset + prim));
+        const double2 a0 = __ldg(r), a1 = __ldg(r + 1), a2 = __ldg(r + 2), a3 = __ldg(r + 3), a4 = __ldg(r + 4);
+        t.p0 = mk3(a0.x, a0.y, a1.x); t.p1 = mk3(a1.y, a2.x, a2.y); t.p2 = mk3(a3.x, a3.y, a4.x);
+        if (want_normals) {
+            const double2 b5 = __ldg(r + 5), b6 = __ldg(r + 6), b7 = __ldg(r + 7), b8 = __ldg(r + 8);
+            t.n0 = mk3(a4.y, b5.x, b5.y); t.n1 = mk3(b6.x, b6.y, b7.x); t.n2 = mk3(b7.y, b8.x, b8.y);
+        }
+        if (want_uvs) {
+            const double2 c9 = __ldg(r + 9), c10 = __ldg(r + 10), c11 = __ldg(r + 11);
+            t.uv0 = mk2(c9.x, c9.y); t.uv1 = mk2(c10.x, c10.y); t.uv2 = mk2(c11.x, c11.y);
+        }
+        return t;
+    }
+    const int *ip = sc.indices + 3 * ((size_t)s.triangle_offset + prim);
+    const int i0 = __ldg(ip), i1 = __ldg(ip + 1), i2 = __ldg(ip + 2);
+    const size_t vb = s.vertex_offset;
+    t.p0 = load3(sc.positions, vb + i0); t.p1 = load3(sc.positions, vb + i1); t.p2 = load3(sc.positions, vb + i2);
+    if (want_normals) { t.n0 = load3(sc.normals, vb + i0); t.n1 = load3(sc.normals, vb + i1); t.n2 = load3(sc.normals, vb + i2); }
+    if (want_uvs) { t.uv0 = load2(sc.uvs, vb + i0); t.uv1 = load2(sc.uvs, vb + i1); t.uv2 = load2(sc.uvs, vb + i2); }
+    return t;
+}
+
 LJ_D ShadingInfo shading_info_mesh(const DScene &sc, const lj_shape &s, const PathVertex &vertex) {
-    const int *ip = sc.indices + 3 * ((size_t)s.triangle_offset + vertex.primitive_id);
-    int i0 = __ldg(ip), i1 = __ldg(ip + 1), i2 = __ldg(ip + 2);
-    size_t vb = s.vertex_offset;
+    const TriVerts tv = load_tri_verts(sc, s, vertex.primitive_id, s.has_normals != 0, s.has_uvs != 0);
     d2 uv0, uv1, uv2;
     if (s.has_uvs) {
-        uv0 = load2(sc.uvs, vb + i0); uv1 = load2(sc.uvs, vb + i1); uv2 = load2(sc.uvs, vb + i2);
+        uv0 = tv.uv0; uv1 = tv.uv1; uv2 = tv.uv2;
     } else {
         uv0 = mk2(0, 0); uv1 = mk2(1, 0); uv2 = mk2(1, 1);
     }
     d2 uv = (1 - vertex.st.x - vertex.st.y) * uv0 + vertex.st.x * uv1 + vertex.st.y * uv2;
-    d3 p0 = load3(sc.positions, vb + i0), p1 = load3(sc.positions, vb + i1), p2 = load3(sc.positions, vb + i2);
+    d3 p0 = tv.p0, p1 = tv.p1, p2 = tv.p2;
     d2 duvds = uv2 - uv0;
     d2 duvdt = uv2 - uv1;
     double det = duvds.x * duvdt.y - duvdt.x * duvds.y;
@@ -137,7 +178,7 @@ LJ_D ShadingInfo shading_info_mesh(const DScene &sc, const lj_shape &s, const Pa
     double mean_curvature = 0;
     d3 tangent, bitangent;
     if (s.has_normals) {
-        d3 n0 = load3(sc.normals, vb + i0), n1 = load3(sc.normals, vb + i1), n2 = load3(sc.normals, vb + i2);
+        d3 n0 = tv.n0, n1 = tv.n1, n2 = tv.n2;
         shading_normal = normalize((1 - vertex.st.x - vertex.st.y) * n0 + vertex.st.x * n1 + vertex.st.y * n2);
         tangent = normalize(dpdu - shading_normal * dot(shading_normal, dpdu));
         d3 dnds = n2 - n0;
@@ -197,9 +238,8 @@ LJ_D PointAndNormal sample_point_on_shape(const DScene &sc, const lj_shape &s, d
     PointAndNormal pn;
     if (s.kind == LJ_SHAPE_MESH) {
         int tri = sample_table1d(sc.tables + s.tri_cdf_offset, (int)s.num_triangles, w);
-        const int *ip = sc.indices + 3 * ((size_t)s.triangle_offset + tri);
-        size_t vb = s.vertex_offset;
-        d3 v0 = load3(sc.positions, vb + __ldg(ip)), v1 = load3(sc.positions, vb + __ldg(ip + 1)), v2 = load3(sc.positions, vb + __ldg(ip + 2));
+        const TriVerts tv = load_tri_verts(sc, s, tri, false, false);
+        d3 v0 = tv.p0, v1 = tv.p1, v2 = tv.p2;
         d3 e1 = v1 - v0, e2 = v2 - v0;
         double a = sqrt(clampd(uv.x, 0.0, 1.0));
         double b1 = 1 - a;
