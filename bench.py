@@ -359,16 +359,27 @@ def roofline_block(scene, rp, stage, rays_by_type, iterations, peak, which, scra
     achieved = n_closest * bytes_ray / ext_s * 1e-9 if ext_s > 0 else None
     sh = max(ct.rays_shadow, 1)
     step_ms = sum(stage.values())
+    issue = None
     traffic = None
     try:   # dram__bytes_read.sum + dram__bytes_write.sum of one `ncu --set full` capture of this kernel (profiles/)
         # (the captured launch is an early, larger one: its bytes are scaled to the average launch by the ratio of the
         #  launch-list average duration to the captured launch's duration -- tools/summarize_profiles.py)
         t = json.load(open(os.path.join(ROOT, "profiles", "traffic.json")))["k_wf_extend<0>"]
         traffic = t.get("dram_bytes_per_avg_launch", t["dram_bytes_per_launch"])
+        if t.get("warp_inst_per_launch") and t.get("launch_ms"):
+            # the ceiling that actually binds this kernel (the BVH is L2-resident): warp instructions issued per second
+            # against SMs x 4 schedulers x clock, and how many of the 32 lanes an issued instruction keeps busy
+            sm_count, clock_hz = 148, 1.965e9
+            per_s = t["warp_inst_per_launch"] / (t["launch_ms"] * 1e-3)
+            issue = {"warp_inst_per_s": per_s, "peak_warp_inst_per_s": sm_count * 4 * clock_hz, "frac": per_s / (sm_count * 4 * clock_hz),
+                     "lanes_per_inst": t.get("lanes_per_inst"), "lane_frac": (t.get("lanes_per_inst") or 0) / 32.0,
+                     "useful_lane_issue_frac": per_s / (sm_count * 4 * clock_hz) * (t.get("lanes_per_inst") or 0) / 32.0,
+                     "issue_active_pct": t.get("issue_active_pct"), "l2_hit_pct": t.get("l2_hit_pct"), "l1_hit_pct": t.get("l1_hit_pct"),
+                     "registers": t.get("registers"), "source": "profiles/" + t.get("capture", "") + " (one ncu --set full launch, under the profiler's serialisation)"}
     except Exception:
         pass
     return {"bound": "hbm", "kernel": "k_wf_extend<false>", "achieved": achieved, "peak": peak, "unit": "GB/s",
-            "frac": achieved / peak if achieved else None, "traffic": traffic, "peak_source": which,
+            "frac": achieved / peak if achieved else None, "traffic": traffic, "issue": issue, "peak_source": which,
             "bytes_per_ray": bytes_ray, "nodes_per_ray": nodes_per_ray, "prims_per_ray": prims_per_ray,
             "launches": int(iterations), "avg_launch_ms": stage["extend_ms"] / max(iterations, 1),
             "bytes_per_launch": n_closest * bytes_ray / max(iterations, 1),

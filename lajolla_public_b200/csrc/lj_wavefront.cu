@@ -49,7 +49,7 @@ __global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n
         int s = tr.sample + wp.map.K;
         int pix, x, y;
         const bool on_film = slot_pixel(wp.map, slot, pix, x, y);
-        if (s >= s_end || !on_film) continue;                   // slot exhausted
+        if (s >= s_end || !on_film) { wp.hit[slot].geom = -2; continue; }   // slot exhausted: never traced again (see k_wf_shade, slot order)
         int w = sc.camera.width, h = sc.camera.height;
         Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)wp.map.npix_total + (unsigned long long)pix);
         double u_first = pcg_real(rng), u_second = pcg_real(rng);   // right-to-left argument evaluation, see lj_path.cuh
@@ -161,76 +161,91 @@ LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const P
 #ifndef LJ_SHADE_MIN_BLOCKS
 #define LJ_SHADE_MIN_BLOCKS 4
 #endif
+// One path vertex: finish the previous bounce with the new hit (emission + MIS, Russian roulette), then NEE + BSDF
+// sampling at the new vertex (path_tracing.h:58-61, :96-322).  Called by the lanes of a warp whose slot has a hit.
 template <int KIND>
-__global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc, WfPool wp, int n_upper) {
-    int n = min(n_upper, wp.counts[Q_KIND0 + KIND]);
-    const int *queue = wp.q_kind[KIND];
-    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        // lanes that entered this iteration together; __syncwarp(together) below forces them to
-        // reconverge after short divergent blocks (the compiler otherwise runs the long common
-        // tail once per diverged group: 1.7x the instructions, seen in profiles/r01c)
-        const unsigned together = __activemask();
-        int slot = queue[i];
-        RayRec rr = wp.ray[slot];
-        ThrRec tr = wp.thr[slot];
-        RadRec ra = wp.rad[slot];
-        HitRec hr = wp.hit[slot];
-        Pcg32 rng; rng.state = ra.rng;
-        rng.inc = (slot_stream(wp.map, slot, tr.sample) << 1u) | 1u;
-        Ray ray = make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), 0, 0);
-        d3 throughput = mk3(tr.tx, tr.ty, tr.tz), radiance = mk3(ra.rx, ra.ry, ra.rz);
-        Hit h; h.t = hr.t; h.u = hr.u; h.v = hr.v; h.geom = hr.geom; h.prim = hr.prim; h.ngx = hr.ngx; h.ngy = hr.ngy; h.ngz = hr.ngz;
-        bool primary = tr.nv == 2;
-        RayDiff rd; rd.radius = 0; rd.spread = primary ? rr.spread : 0.0;   // bounce rays: intersect(scene, bsdf_ray) default differential
-        PathVertex vertex = make_vertex(sc, ray, h, rd);
-        bool alive = true;
-        bool is_light = sc.shapes[vertex.shape_id].area_light_id >= 0;
-        if (primary) {
-            if (is_light) radiance += throughput * vertex_emission(sc, vertex, -ray.dir);   // path_tracing.h:58-61
-            tr.nv = 3;
-        } else {
-            // finish the previous bounce with the new vertex (path_tracing.h:242-322)
-            d3 f = mk3(tr.fx, tr.fy, tr.fz);
-            double G = fabs(dot(ray.dir, vertex.geometry_normal)) / distance_squared(vertex.position, ray.org);
-            double p2 = tr.p2 * G;
-            if (is_light) {
-                d3 L = vertex_emission(sc, vertex, -ray.dir);
-                d3 C2 = G * f * L;
-                int lid = sc.shapes[vertex.shape_id].area_light_id;
-                PointAndNormal lp; lp.position = vertex.position; lp.normal = vertex.geometry_normal;
-                double p1 = __ldg(sc.light_pmf + lid) * pdf_point_on_light(sc, sc.lights[lid], lp, ray.org);
-                double w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
-                C2 = C2 / p2;
-                radiance += throughput * C2 * w2;
-            }
-            double rr_prob = 1;
-            if (tr.nv - 1 >= sc.options.rr_depth) {
-                rr_prob = lmin(max3((1 / rr.eta_scale) * throughput), 0.95);
-                if (pcg_real(rng) > rr_prob) alive = false;
-            }
-            if (alive) {
-                throughput = throughput * (G * f) / (p2 * rr_prob);
-                tr.nv += 1;
-            }
+LJ_D void shade_slot(const DScene &sc, const WfPool &wp, const int slot, const HitRec &hr) {
+    // lanes that entered this iteration together; __syncwarp(together) below forces them to
+    // reconverge after short divergent blocks (the compiler otherwise runs the long common
+    // tail once per diverged group: 1.7x the instructions, seen in profiles/r01c)
+    const unsigned together = __activemask();
+    RayRec rr = wp.ray[slot];
+    ThrRec tr = wp.thr[slot];
+    RadRec ra = wp.rad[slot];
+    Pcg32 rng; rng.state = ra.rng;
+    rng.inc = (slot_stream(wp.map, slot, tr.sample) << 1u) | 1u;
+    Ray ray = make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), 0, 0);
+    d3 throughput = mk3(tr.tx, tr.ty, tr.tz), radiance = mk3(ra.rx, ra.ry, ra.rz);
+    Hit h; h.t = hr.t; h.u = hr.u; h.v = hr.v; h.geom = hr.geom; h.prim = hr.prim; h.ngx = hr.ngx; h.ngy = hr.ngy; h.ngz = hr.ngz;
+    bool primary = tr.nv == 2;
+    RayDiff rd; rd.radius = 0; rd.spread = primary ? rr.spread : 0.0;   // bounce rays: intersect(scene, bsdf_ray) default differential
+    PathVertex vertex = make_vertex(sc, ray, h, rd);
+    bool alive = true;
+    bool is_light = sc.shapes[vertex.shape_id].area_light_id >= 0;
+    if (primary) {
+        if (is_light) radiance += throughput * vertex_emission(sc, vertex, -ray.dir);   // path_tracing.h:58-61
+        tr.nv = 3;
+    } else {
+        // finish the previous bounce with the new vertex (path_tracing.h:242-322)
+        d3 f = mk3(tr.fx, tr.fy, tr.fz);
+        double G = fabs(dot(ray.dir, vertex.geometry_normal)) / distance_squared(vertex.position, ray.org);
+        double p2 = tr.p2 * G;
+        if (is_light) {
+            d3 L = vertex_emission(sc, vertex, -ray.dir);
+            d3 C2 = G * f * L;
+            int lid = sc.shapes[vertex.shape_id].area_light_id;
+            PointAndNormal lp; lp.position = vertex.position; lp.normal = vertex.geometry_normal;
+            double p1 = __ldg(sc.light_pmf + lid) * pdf_point_on_light(sc, sc.lights[lid], lp, ray.org);
+            double w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
+            C2 = C2 / p2;
+            radiance += throughput * C2 * w2;
         }
-        __syncwarp(together);
-        const int max_depth = sc.options.max_depth;
-        if (alive && !(max_depth == -1 || tr.nv <= max_depth + 1)) alive = false;
-        bool pushed_shadow = false;
-        if (alive) alive = bounce_at_vertex<KIND>(sc, wp, slot, vertex, -ray.dir, rng, throughput, rr, tr, pushed_shadow);
-        if (!alive) {
-            if (!pushed_shadow) { terminate_path(wp, slot, tr.sample, radiance); continue; }
-            // the path ends here but its last NEE term is still in the shadow queue: park the
-            // radiance and let the finish stage (after the shadow stage) do the accumulation
-            ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
-            wp.rad[slot] = ra;
-            wp.q_finish[queue_push_uniform(&wp.counts[Q_FINISH])] = slot;
-            continue;
+        double rr_prob = 1;
+        if (tr.nv - 1 >= sc.options.rr_depth) {
+            rr_prob = lmin(max3((1 / rr.eta_scale) * throughput), 0.95);
+            if (pcg_real(rng) > rr_prob) alive = false;
         }
-        tr.tx = throughput.x; tr.ty = throughput.y; tr.tz = throughput.z;
+        if (alive) {
+            throughput = throughput * (G * f) / (p2 * rr_prob);
+            tr.nv += 1;
+        }
+    }
+    __syncwarp(together);
+    const int max_depth = sc.options.max_depth;
+    if (alive && !(max_depth == -1 || tr.nv <= max_depth + 1)) alive = false;
+    bool pushed_shadow = false;
+    if (alive) alive = bounce_at_vertex<KIND>(sc, wp, slot, vertex, -ray.dir, rng, throughput, rr, tr, pushed_shadow);
+    if (!alive) {
+        if (!pushed_shadow) { terminate_path(wp, slot, tr.sample, radiance); return; }
+        // the path ends here but its last NEE term is still in the shadow queue: park the
+        // radiance and let the finish stage (after the shadow stage) do the accumulation
         ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
-        wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
-        push_extend(wp, slot, make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), sc.eps, INFINITY));
+        wp.rad[slot] = ra;
+        wp.q_finish[queue_push_uniform(&wp.counts[Q_FINISH])] = slot;
+        return;
+    }
+    tr.tx = throughput.x; tr.ty = throughput.y; tr.tz = throughput.z;
+    ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
+    wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
+    push_extend(wp, slot, make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), sc.eps, INFINITY));
+}
+
+// Two ways to walk the work.  Queue order (SLOTS = false): the slots the extend stage put into this kind's queue.
+// Slot order (SLOTS = true, scenes with ONE material kind): every live slot is traced in every iteration, so the
+// kernel walks the pool itself and skips slots without a hit (missed: geom -1, exhausted: geom -2) -- the 64-byte
+// slot records are then read and written fully coalesced (2 KB contiguous per warp) instead of gathered through the
+// queue, and the queue read drops out of the dependent-load chain.  Same per-slot arithmetic either way.
+template <int KIND, bool SLOTS>
+__global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc, WfPool wp, int n_upper) {
+    const int n = SLOTS ? wp.capacity : min(n_upper, wp.counts[Q_KIND0 + KIND]);
+    const int *queue = wp.q_kind[KIND];
+    const int lane = threadIdx.x & 31;
+    for (int base = blockIdx.x * blockDim.x + threadIdx.x - lane; base < n; base += gridDim.x * blockDim.x) {
+        const int i = base + lane;
+        int slot = -1; HitRec hr; hr.geom = -1;
+        if (i < n) { slot = SLOTS ? i : queue[i]; hr = wp.hit[slot]; }
+        if (hr.geom >= 0) shade_slot<KIND>(sc, wp, slot, hr);
+        __syncwarp();       // the warp walks the range in lockstep: lanes without work wait here
     }
 }
 
@@ -268,10 +283,12 @@ __global__ void __launch_bounds__(128) k_wf_miss(DScene sc, WfPool wp, int n_upp
 }
 
 template <int KIND>
-void launch_shade(const DScene &d, const WfPool &wp, int n_upper, int grid_cap) {
-    int grid = (n_upper + 127) / 128;
+void launch_shade(const DScene &d, const WfPool &wp, int n_upper, int grid_cap, bool slot_order) {
+    int grid = ((slot_order ? wp.capacity : n_upper) + 127) / 128;
     if (grid > grid_cap) grid = grid_cap;
-    k_wf_shade<KIND><<<grid, 128>>>(d, wp, n_upper);
+    if (grid < 1) grid = 1;
+    if (slot_order) k_wf_shade<KIND, true><<<grid, 128>>>(d, wp, n_upper);
+    else k_wf_shade<KIND, false><<<grid, 128>>>(d, wp, n_upper);
 }
 
 } // namespace
@@ -346,6 +363,12 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     k_wf_init<<<sm * 8, 256>>>(wp, rl.s_begin);
     if (cudaGetLastError() != cudaSuccess) { cleanup(); lj_set_error("wavefront: init launch failed"); return LJ_ECUDA; }
     int n_regen = capacity, n_ext = 0;      // queue sizes after the last retired iteration
+    int n_kinds = 0;
+    for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) n_kinds += kind_present[k] ? 1 : 0;
+    const bool slots_ok = n_kinds == 1 && !getenv("LJ_SHADE_QUEUE");
+    // slot order while at least this share of the pool is live (below it the idle lanes of dead slots cost more than
+    // the coalesced records save: cbox, whose paths die early, and the tail of every render)
+    const int slots_min_live_pct = env_int("LJ_SHADE_SLOTS_MIN_LIVE_PCT", 85);
     unsigned long long launches = 2, rays_primary = 0, rays_ext = 0, rays_shadow = 0;
     unsigned long long launched = 0, retired = 0;
     auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
@@ -362,16 +385,18 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         if (stage_timing) cudaEventRecord(e[1]);
         lj_wf_launch_extend(d, wp, upper, trav, tune_ext, counting, grid_for(upper, trace_grid_cap));
         if (stage_timing) cudaEventRecord(e[2]);
+        // slot order while most of the pool is live (the last sizes the host has seen), queue order in the tail
+        const bool slot_order = slots_ok && (long long)(n_ext + n_regen) * 100 >= (long long)capacity * slots_min_live_pct;
         k_wf_miss<<<grid_for(upper, shade_grid_cap), 128>>>(d, wp, upper);
-        if (kind_present[0]) launch_shade<0>(d, wp, upper, shade_grid_cap);
-        if (kind_present[1]) launch_shade<1>(d, wp, upper, shade_grid_cap);
-        if (kind_present[2]) launch_shade<2>(d, wp, upper, shade_grid_cap);
-        if (kind_present[3]) launch_shade<3>(d, wp, upper, shade_grid_cap);
-        if (kind_present[4]) launch_shade<4>(d, wp, upper, shade_grid_cap);
-        if (kind_present[5]) launch_shade<5>(d, wp, upper, shade_grid_cap);
-        if (kind_present[6]) launch_shade<6>(d, wp, upper, shade_grid_cap);
-        if (kind_present[7]) launch_shade<7>(d, wp, upper, shade_grid_cap);
-        if (kind_present[8]) launch_shade<8>(d, wp, upper, shade_grid_cap);
+        if (kind_present[0]) launch_shade<0>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[1]) launch_shade<1>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[2]) launch_shade<2>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[3]) launch_shade<3>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[4]) launch_shade<4>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[5]) launch_shade<5>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[6]) launch_shade<6>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[7]) launch_shade<7>(d, wp, upper, shade_grid_cap, slot_order);
+        if (kind_present[8]) launch_shade<8>(d, wp, upper, shade_grid_cap, slot_order);
         if (stage_timing) cudaEventRecord(e[3]);
         lj_wf_launch_shadow(d, wp, upper, trav, tune_sh, counting, grid_for(upper, trace_grid_cap));
         k_wf_finish<<<grid_for(upper, shade_grid_cap), 128>>>(wp, upper);

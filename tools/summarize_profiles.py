@@ -97,6 +97,16 @@ def full(tag, src, out):
                       + float(d["dram__bytes_write.sum"][0].replace(",", "")) * {"Mbyte": 1e6, "Gbyte": 1e9, "Kbyte": 1e3, "byte": 1}[d["dram__bytes_write.sum"][1]])
                 TRAFFIC[short(d["Kernel Name"][0])] = {"dram_bytes_per_launch": tr, "capture": f"{tag}_{name}.md",
                                                        "launch_ms": float(d["gpu__time_duration.sum"][0].replace(",", "")) * {"ms": 1, "us": 1e-3, "s": 1e3, "ns": 1e-6}[d["gpu__time_duration.sum"][1]]}
+                def num(k):
+                    return float(d[k][0].replace(",", "")) if k in d else None
+                ent = TRAFFIC[short(d["Kernel Name"][0])]
+                # the issue-slot view of the same launch (bench.py `roofline.issue`): warp instructions, lanes per instruction
+                ent.update({"warp_inst_per_launch": num("smsp__inst_executed.sum"),
+                            "lanes_per_inst": num("smsp__thread_inst_executed_per_inst_executed.ratio"),
+                            "issue_active_pct": num("smsp__issue_active.avg.pct_of_peak_sustained_active"),
+                            "warps_active_pct": num("sm__warps_active.avg.pct_of_peak_sustained_active"),
+                            "l2_hit_pct": num("lts__t_sector_hit_rate.pct"), "l1_hit_pct": num("l1tex__t_sector_hit_rate.pct"),
+                            "registers": num("launch__registers_per_thread")})
             except Exception as e:
                 print("traffic:", e)
             f.write("\nWarp stall reasons (% of warp-active cycles per issue slot):\n\n| reason | pct |\n|---|---|\n")
