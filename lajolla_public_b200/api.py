@@ -120,8 +120,9 @@ def load_library():
     lib = C.CDLL(p)
     lib.lj_last_error.restype = C.c_char_p
     lib.lj_init.argtypes = [C.c_int, C.POINTER(C.c_void_p)]
-    lib.lj_init_devices.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
-    lib.lj_ctx_device_count.argtypes = [C.c_void_p]
+    if hasattr(lib, "lj_init_devices"):      # (absent from older builds loaded through LJ_LIB for before/after runs)
+        lib.lj_init_devices.argtypes = [C.POINTER(C.c_int), C.c_int, C.POINTER(C.c_void_p)]
+        lib.lj_ctx_device_count.argtypes = [C.c_void_p]
     lib.lj_shutdown.argtypes = [C.c_void_p]
     lib.lj_shutdown.restype = None
     lib.lj_scene_create.argtypes = [C.c_void_p, C.c_void_p, C.POINTER(C.c_void_p)]
@@ -143,7 +144,8 @@ def load_library():
     lib.lj_image_encode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.lj_image_write.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32]
     lib.lj_accum_finalize.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
-    lib.lj_accum_finalize_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
+    if hasattr(lib, "lj_accum_finalize_static"):
+        lib.lj_accum_finalize_static.argtypes = [C.c_void_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p]
     lib.lj_accum_encode.argtypes = [C.c_void_p, C.c_int32, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_void_p, C.c_uint64, C.POINTER(C.c_uint64)]
     lib.lj_accum_write.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32]
     lib.lj_accum_save.argtypes = [C.c_void_p, C.c_char_p, C.c_void_p, C.c_int32, C.c_int32, C.c_int32, C.c_int32]
@@ -179,7 +181,7 @@ class LajollaGPU:
         else:
             _check(self.lib, self.lib.lj_init(int(device), C.byref(self.handle)), "lj_init")
         self.device = device
-        self.n_devices = int(self.lib.lj_ctx_device_count(self.handle))
+        self.n_devices = int(self.lib.lj_ctx_device_count(self.handle)) if hasattr(self.lib, "lj_ctx_device_count") else 1
 
     def load_scene(self, blob_path, res=None, spp=None, integrator=None):
         return Scene(self, blob_path, res=res, spp=spp, integrator=integrator)

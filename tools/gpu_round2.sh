@@ -12,6 +12,8 @@ timeout 600 python bench.py --impl reference --steps 2 --warmup 1 > gpurun_out/b
 timeout 300 python tools/profile_stages.py sponza 64 > gpurun_out/stages_sponza.json 2>&1
 timeout 900 python tools/bench_scenes.py --cpu > gpurun_out/scenes.json 2> gpurun_out/scenes.err; echo "scenes rc=$?"
 timeout 300 python tools/step_overhead.py > gpurun_out/step_overhead.log 2>&1; echo "overhead rc=$?"
+# the same probe on the round-1 library (commit 70eb13a, built by hand into tools/variants/): before / after of the host loop
+if [ -f tools/variants/lib_r01.so ]; then LJ_LIB=$PWD/tools/variants/lib_r01.so LJ_OVERHEAD_TAG=_r01 timeout 300 python tools/step_overhead.py > gpurun_out/step_overhead_r01.log 2>&1; echo "overhead r01 rc=$?"; fi
 timeout 300 python tools/bvh_trace.py sponza matpreview cbox > gpurun_out/bvh_trace.log 2>&1
 if [ $rc -eq 0 ]; then
   NB="python bench.py --steps 1 --warmup 1 --no-cpu-baseline --no-strong"
@@ -22,3 +24,9 @@ if [ $rc -eq 0 ]; then
   timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_vol_track -s 20 -c 1 -o gpurun_out/vol_track_full -f \
       python tools/sweep_pool.py hetvol 8 8388608 > gpurun_out/ncu_full_track.log 2>&1; echo "ncu track rc=$?"
 fi
+# the reports are too big to travel (gpurun_out is capped at 64 MiB): summarise them here, keep only the summaries
+mkdir -p gpurun_out/profiles_r02
+python tools/summarize_profiles.py r02 gpurun_out gpurun_out/profiles_r02 > gpurun_out/summarize.log 2>&1; echo "summarize rc=$?"
+for k in extend shade; do ncu -i gpurun_out/${k}_full.ncu-rep --page source --csv > gpurun_out/${k}_source.csv 2>/dev/null; gzip -f gpurun_out/${k}_source.csv; done
+rm -f gpurun_out/*.ncu-rep
+du -sh gpurun_out

@@ -51,7 +51,8 @@ def main():
                 print(key, json.dumps({k: (round(v, 3) if isinstance(v, float) else v) for k, v in out[key].items() if k != "wall_all"}), flush=True)
         sc.close()
     gpu.close()
-    json.dump(out, open(os.path.join(ROOT, "gpurun_out", "step_overhead.json"), "w"), indent=1)
+    tag = os.environ.get("LJ_OVERHEAD_TAG", "")
+    json.dump(out, open(os.path.join(ROOT, "gpurun_out", f"step_overhead{tag}.json"), "w"), indent=1)
 
 
 if __name__ == "__main__":

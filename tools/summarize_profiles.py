@@ -3,7 +3,7 @@
   <tag>_launches.md      per-kernel totals of the ncu launch list (gpu__time_duration.sum) of the bench command
   <tag>_<kernel>_full.md key counters of the `ncu --set full` capture of one launch of a kernel
   <tag>_bench.json       the bench lines of the same visit
-usage: tools/summarize_profiles.py r01 [gpurun_out]"""
+usage: tools/summarize_profiles.py r01 [gpurun_out [output dir]]"""
 import collections
 import csv
 import json
@@ -87,8 +87,10 @@ def full(tag, src, out):
         name = rep[:-8]
         with open(os.path.join(out, f"{tag}_{name}.md"), "w") as f:
             f.write(f"# {tag}: `ncu --set full --clock-control none` of one launch of `{short(d['Kernel Name'][0])}`\n\n")
-            f.write("Captured inside `python bench.py --steps 1 --warmup 1` (sponza 768x575, 64 spp, wavefront engine); "
-                    "a mid-render launch (`-s 6 -c 1`).\n\n| metric | value | unit |\n|---|---|---|\n")
+            what = ("`python tools/sweep_pool.py hetvol 8 8388608` (hetvol 768x576, 8 spp, volumetric wavefront engine); launch `-s 20 -c 1`"
+                    if "track" in name else
+                    "`python bench.py --steps 1 --warmup 1` (sponza 768x575, 64 spp, wavefront engine); a mid-render launch (`-s 6 -c 1`)")
+            f.write(f"Captured inside {what}.\n\n| metric | value | unit |\n|---|---|---|\n")
             for k in KEYS:
                 if k in d:
                     f.write(f"| {k} | {d[k][0]} | {d[k][1]} |\n")
@@ -119,7 +121,7 @@ def full(tag, src, out):
 def main():
     tag = sys.argv[1]
     src = sys.argv[2] if len(sys.argv) > 2 else os.path.join(ROOT, "gpurun_out")
-    out = os.path.join(ROOT, "profiles")
+    out = sys.argv[3] if len(sys.argv) > 3 else os.path.join(ROOT, "profiles")
     os.makedirs(out, exist_ok=True)
     launches(tag, src, out)
     full(tag, src, out)
