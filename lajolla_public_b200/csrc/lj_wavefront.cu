@@ -375,9 +375,14 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     bool finished = false;
     int loop_rc = LJ_OK;
     while (!finished) {
+        // Slots only ever leave the pool (exhausted ones at the generate stage), so the live count of the last retired
+        // iteration bounds every queue of every later iteration: grids are sized from it even while iterations are in
+        // flight (all stage kernels are grid-stride / work-counter loops clamped to the device counts, so a bound that
+        // is a few iterations stale costs nothing but a few idle blocks).
         const bool exact = launched == retired;          // nothing in flight: the sizes are the true ones
-        const int regen_upper = exact ? n_regen : capacity;
-        const int upper = exact ? n_ext + n_regen : capacity;
+        const int live = n_ext + n_regen > capacity ? capacity : n_ext + n_regen;
+        const int regen_upper = exact ? n_regen : live;
+        const int upper = live;
         const int ring_slot = (int)(launched % depth);
         cudaEvent_t *e = ev[ring_slot];
         if (stage_timing) cudaEventRecord(e[0]);
