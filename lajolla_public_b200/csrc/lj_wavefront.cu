@@ -366,9 +366,11 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     int n_kinds = 0;
     for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) n_kinds += kind_present[k] ? 1 : 0;
     const bool slots_ok = n_kinds == 1 && !getenv("LJ_SHADE_QUEUE");
-    // slot order while at least this share of the pool is live (below it the idle lanes of dead slots cost more than
-    // the coalesced records save: cbox, whose paths die early, and the tail of every render)
-    const int slots_min_live_pct = env_int("LJ_SHADE_SLOTS_MIN_LIVE_PCT", 85);
+    // slot order while at least this share of the pool's slots had a hit in the last iteration the host has seen (below it
+    // the idle lanes of missed / exhausted slots cost more than the coalesced records save: open scenes such as cbox, renders
+    // without regeneration, and the tail of every render)
+    const int slots_min_live_pct = env_int("LJ_SHADE_SLOTS_MIN_LIVE_PCT", 95);
+    int n_hits = capacity;
     unsigned long long launches = 2, rays_primary = 0, rays_ext = 0, rays_shadow = 0;
     unsigned long long launched = 0, retired = 0;
     auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
@@ -391,7 +393,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         lj_wf_launch_extend(d, wp, upper, trav, tune_ext, counting, grid_for(upper, trace_grid_cap));
         if (stage_timing) cudaEventRecord(e[2]);
         // slot order while most of the pool is live (the last sizes the host has seen), queue order in the tail
-        const bool slot_order = slots_ok && (long long)(n_ext + n_regen) * 100 >= (long long)capacity * slots_min_live_pct;
+        const bool slot_order = slots_ok && (long long)n_hits * 100 >= (long long)capacity * slots_min_live_pct;
         k_wf_miss<<<grid_for(upper, shade_grid_cap), 128>>>(d, wp, upper);
         if (kind_present[0]) launch_shade<0>(d, wp, upper, shade_grid_cap, slot_order);
         if (kind_present[1]) launch_shade<1>(d, wp, upper, shade_grid_cap, slot_order);
@@ -414,7 +416,10 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         // retire what has completed; block only when the ring is full
         while (retired < launched) {
             const int rs = (int)(retired % depth);
-            if (launched - retired < (unsigned long long)depth && cudaEventQuery(done[rs]) == cudaErrorNotReady) break;
+            // how far the host runs ahead: one speculative iteration while iterations are large (it hides the read-back
+            // and costs at most one empty iteration at the end), the full ring once they are small and launch-bound
+            const unsigned long long ahead = (n_ext + n_regen) >= (1 << 19) ? (depth < 2 ? depth : 2) : depth;
+            if (launched - retired < ahead && cudaEventQuery(done[rs]) == cudaErrorNotReady) break;
             const cudaError_t ce = cudaEventSynchronize(done[rs]);
             if (ce != cudaSuccess) { lj_set_error("wavefront iteration failed: %s", cudaGetErrorString(ce)); loop_rc = LJ_ECUDA; finished = true; break; }
             const int *h_counts = h_ring + rs * Q_COUNT;
@@ -435,6 +440,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
                         (unsigned long long)st->iterations, traced, n_regen, h_counts[Q_SHADOW], h_counts[Q_EXT], h_counts[Q_REGEN], ms_e, ms_s, ms_h);
             n_regen = h_counts[Q_REGEN];
             n_ext = h_counts[Q_EXT];
+            n_hits = traced - h_counts[Q_MISS];
             st->iterations++;
             retired++;
             // (slots whose samples are used up sit in the regeneration queue once more: that iteration generates
