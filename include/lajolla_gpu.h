@@ -165,7 +165,8 @@ typedef struct lj_render_params {
     int32_t rng_mode;              /* LJ_RNG_* */
     int32_t engine;                /* LJ_ENGINE_*; mode A always runs tile-serial */
     int32_t sample_begin, sample_end;   /* spp slice [begin,end) for mode B; 0,0 => [0,spp) */
-    int32_t tile_rank, tile_world;      /* 16x16 tiles dealt round-robin: tile_id % world == rank; world 0 => all */
+    int32_t tile_rank, tile_world;      /* this call renders the 16x16 tiles dealt to `rank` of `world` (tile (tx, ty) belongs to rank
+                                           (ty*ntx + (tx + 3 ty) % ntx) % world: row-rotated round robin); world 0 => all tiles */
     int32_t max_depth_override;    /* -100 => scene options */
     int32_t paths_in_flight;       /* wavefront pool size, 0 => auto */
     int32_t flags;                 /* bit0: count traversal steps (nodes / prims per ray); bit1: per-stage CUDA-event times */
@@ -174,7 +175,7 @@ typedef struct lj_render_params {
 
 /* Work split of ONE render over the devices of a multi-device context; the scene is replicated, every
  * device renders its share into its own f64 sums, and the sums are added with one NCCL reduce to the first device.
- *   TILES  the 16x16 tiles of render.cpp:75-82 dealt round-robin (tile id % n_devices): disjoint pixels, so the reduced
+ *   TILES  the 16x16 tiles of render.cpp:75-82 dealt round-robin, each tile row rotated against the one above (see tile_rank): disjoint pixels, so the reduced
  *          image is bit-identical to the one-device image for every device count and every integrator / RNG mode;
  *   SPP    device i renders a contiguous slice of the samples of EVERY pixel (balanced when cost is spatially skewed);
  *          needs per-sample streams (LJ_RNG_SAMPLE_STREAMS) and a sampling integrator, otherwise TILES is used.

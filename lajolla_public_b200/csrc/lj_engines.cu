@@ -31,8 +31,8 @@ __global__ void k_tiles_mode_a(DScene sc, int ntx, int nty, int spp, int tile_ra
                                double *sum, unsigned long long *counters) {
     int tile = blockIdx.x * blockDim.x + threadIdx.x;
     if (tile >= ntx * nty) return;
-    if (tile_world > 0 && (tile % tile_world) != tile_rank) return;
     int tx = tile % ntx, ty = tile / ntx;
+    if (tile_world > 0 && (tile_dealt_index(tx, ty, ntx) % tile_world) != tile_rank) return;
     Pcg32 rng = pcg_init((uint64_t)(ty * ntx + tx));
     int w = sc.camera.width, h = sc.camera.height;
     int x0 = tx * 16, x1 = min(x0 + 16, w), y0 = ty * 16, y1 = min(y0 + 16, h);
@@ -64,7 +64,7 @@ __global__ void k_mega_mode_b(DScene sc, int ntx, int s_begin, int s_end, int K,
     d3 radiance = mk3(0.0);
     RayCounters rc; rc.primary = rc.extension = rc.shadow = 0;
     bool mine = true;
-    if (tile_world > 0) { int tile = (y / 16) * ntx + (x / 16); mine = (tile % tile_world) == tile_rank; }
+    if (tile_world > 0) mine = (tile_dealt_index(x / 16, y / 16, ntx) % tile_world) == tile_rank;
     if (mine) {
         for (int s = s_begin + k; s < s_end; s += K) {
             Pcg32 rng = pcg_init((uint64_t)s * (uint64_t)npix + (uint64_t)pix);
@@ -151,7 +151,7 @@ __global__ void k_aux(DScene sc, int ntx, int tile_rank, int tile_world, double 
     int w = sc.camera.width, h = sc.camera.height;
     if (pix >= w * h) return;
     int x = pix % w, y = pix / w;
-    if (tile_world > 0 && (((y / 16) * ntx + (x / 16)) % tile_world) != tile_rank) {     // another rank's tile
+    if (tile_world > 0 && (tile_dealt_index(x / 16, y / 16, ntx) % tile_world) != tile_rank) {     // another rank's tile
         sum[3 * (size_t)pix] = 0; sum[3 * (size_t)pix + 1] = 0; sum[3 * (size_t)pix + 2] = 0;
         return;
     }

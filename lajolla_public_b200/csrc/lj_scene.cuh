@@ -77,6 +77,14 @@ struct DScene {
     unsigned m15_bits;
 };
 
+// Deal of the 16x16 tiles (render.cpp:75-82) over `world` ranks: tile (tx, ty) gets the dealt index
+// v = ty * ntx + (tx + 3 ty) mod ntx -- each tile row rotated by three more columns than the one above, so that a
+// rank's tiles form diagonals instead of the vertical stripes `tile id mod world` gives whenever world divides the
+// tiles per row (sponza: 48 tiles per row, 8 GPUs) -- and belongs to rank v mod world; v / world numbers a rank's
+// tiles densely.  Any fixed deal keeps the partition bit-identical to one device; this one balances it.
+LJ_HD int tile_dealt_index(int tx, int ty, int ntx) { return ty * ntx + (tx + 3 * ty) % ntx; }
+LJ_HD void tile_from_dealt_index(int v, int ntx, int &tx, int &ty) { ty = v / ntx; tx = (v % ntx + ntx - (3 * ty) % ntx) % ntx; }
+
 // intersection.h:15-35
 struct PathVertex {
     d3 position, geometry_normal;

@@ -78,9 +78,10 @@ struct SlotMap {
 LJ_D bool slot_pixel(const SlotMap &m, int slot, int &pix, int &x, int &y) {
     const int pl = slot % m.npix_local;
     if (m.tile_world <= 0) { pix = pl; x = pl % m.width; y = pl / m.width; return true; }
-    const int tile = (pl >> 8) * m.tile_world + m.tile_rank;
-    x = (tile % m.ntx) * 16 + (pl & 15);
-    y = (tile / m.ntx) * 16 + ((pl >> 4) & 15);
+    int tx, ty;
+    tile_from_dealt_index((pl >> 8) * m.tile_world + m.tile_rank, m.ntx, tx, ty);     // lj_scene.cuh
+    x = tx * 16 + (pl & 15);
+    y = ty * 16 + ((pl >> 4) & 15);
     pix = y * m.width + x;
     return x < m.width && y < m.height;
 }

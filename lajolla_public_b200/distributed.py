@@ -6,8 +6,9 @@ The reference's unit of independent work is the 16x16 tile with its own pcg32 st
 
   "spp"   rank r renders samples [begin_r, end_r) of EVERY pixel (balanced even when cost is
           spatially skewed); the per-pixel sums of all ranks are added.
-  "tiles" tile t belongs to rank t % world; pixels are disjoint, so the reduced image is
-          bit-identical to the 1-GPU image for any world size (adding zeros is exact).
+  "tiles" tile (tx, ty) belongs to rank (ty*ntx + (tx + 3 ty) % ntx) % world (the library's deal: diagonals rather
+          than vertical stripes); pixels are disjoint, so the reduced image is bit-identical to the 1-GPU image for any
+          world size (adding zeros is exact).
 
 There is no data-path exchange other than that single reduction.  The render itself is the
 C-ABI call lj_render_device (include/lajolla_gpu.h); this module only plans the partition and
@@ -57,8 +58,11 @@ def tile_owner_mask(width, height, rank, world):
     import numpy as np
     ntx = (width + TILE - 1) // TILE
     ys, xs = np.mgrid[0:height, 0:width]
-    tile = (ys // TILE) * ntx + (xs // TILE)
-    return (tile % world) == rank if world > 1 else np.ones((height, width), dtype=bool)
+    # the library's deal (tile_dealt_index, csrc/lj_scene.cuh): each tile row rotated by three more columns than the
+    # one above, so a rank's tiles form diagonals rather than vertical stripes
+    ty, tx = ys // TILE, xs // TILE
+    dealt = ty * ntx + (tx + 3 * ty) % ntx
+    return (dealt % world) == rank if world > 1 else np.ones((height, width), dtype=bool)
 
 
 def params_for(part, rng_mode, engine, flags=0):

@@ -1,6 +1,6 @@
 """The work partitions of SURVEY 8(e) on the GPU itself ("no N-way-equals-1-way check on a GPU").
 
-One device: for world in {2, 3, 8} every rank's share (tile id % world == rank, the 16x16 tiles of render.cpp:75-82) is
+One device: for world in {2, 3, 8} every rank's share (the row-rotated round-robin deal of the 16x16 tiles of render.cpp:75-82) is
 rendered into its own f64 sums; their sum must equal the unpartitioned render BIT FOR BIT (the accumulators are laid
 out so that the per-pixel summation order does not depend on the partition or the pool size, lj_wave_common.cuh
 SlotMap).  Sample slices [0,a) [a,b) [b,spp) add up to the full render to within 1 ulp of the f32 image.
@@ -41,6 +41,7 @@ def load(gpu, name, res):
 def test_tile_partition_is_bit_identical(gpu, name, res, spp, engine):
     import torch
     from lajolla_public_b200 import RenderParams, RNG_SAMPLE_STREAMS, ENGINE_MEGAKERNEL, ENGINE_WAVEFRONT
+    from lajolla_public_b200.distributed import tile_owner_mask
     if engine == "megakernel" and name in ("sponza", "hetvol"):
         pytest.skip("whole-path engine covered on the small scenes")
     eng = ENGINE_MEGAKERNEL if engine == "megakernel" else ENGINE_WAVEFRONT
@@ -53,7 +54,10 @@ def test_tile_partition_is_bit_identical(gpu, name, res, spp, engine):
             rays = 0
             for r in range(world):
                 part, st = device_sums(scene, RenderParams(spp=spp, rng_mode=RNG_SAMPLE_STREAMS, engine=eng, tile_rank=r, tile_world=world))
-                # a rank leaves the other ranks' pixels at exactly zero, so adding is exact
+                # a rank leaves the other ranks' pixels at exactly zero, so adding is exact; its own pixels are the ones the
+                # documented deal gives it (distributed.tile_owner_mask restates the library's tile_dealt_index)
+                touched = (part.reshape(scene.height, scene.width, 3) != 0).any(dim=2).cpu().numpy()
+                assert not (touched & ~tile_owner_mask(scene.width, scene.height, r, world)).any()
                 total += part
                 rays += st.rays
             same = bool(torch.equal(total, full))
