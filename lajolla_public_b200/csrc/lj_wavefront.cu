@@ -31,7 +31,56 @@ LJ_D void push_extend(const WfPool &wp, int slot, const Ray &r) {
     wp.ext_slot[pos] = slot;
 }
 
+// Where a stage's outputs go.  QueueSink: the wavefront queues (warp-aggregated pushes; the stage kernels).  LaneSink: the
+// lane's own registers (k_wf_tail, which runs a path to its end in one lane).  The per-slot arithmetic is the same code.
+struct QueueSink {
+    const WfPool &wp;
+    LJ_D QueueSink(const WfPool &w) : wp(w) {}
+    LJ_D void extend(int slot, const Ray &r) { push_extend(wp, slot, r); }
+    LJ_D void shadow(int slot, const RayF &ray, d3 contrib) {
+        ShadowRec s; s.ray = ray; s.cx = contrib.x; s.cy = contrib.y; s.cz = contrib.z; s.slot = slot; s._pad = 0;
+        wp.shadow[queue_push_uniform(&wp.counts[Q_SHADOW])] = s;
+    }
+    LJ_D void terminate(int slot, int sample, d3 radiance) { terminate_path(wp, slot, sample, radiance); }
+    LJ_D void finish(int slot) { wp.q_finish[queue_push_uniform(&wp.counts[Q_FINISH])] = slot; }   // last NEE term still in the shadow queue
+};
+struct LaneSink {
+    const WfPool &wp;
+    int what;                  // 0: path ended and was accumulated, 1: `next` is its extension ray, 2: ended, accumulate after the shadow ray
+    bool has_shadow;
+    RayF next, shadow_ray; double cx, cy, cz;
+    LJ_D LaneSink(const WfPool &w) : wp(w), what(0), has_shadow(false) {}
+    LJ_D void extend(int, const Ray &r) { next = to_rayf(r); what = 1; }
+    LJ_D void shadow(int, const RayF &ray, d3 contrib) { shadow_ray = ray; cx = contrib.x; cy = contrib.y; cz = contrib.z; has_shadow = true; }
+    LJ_D void terminate(int slot, int sample, d3 radiance) {
+        double *a = wp.accum + accum_offset(wp.map, slot, sample);
+        a[0] += radiance.x; a[1] += radiance.y; a[2] += radiance.z;
+        what = 0;
+    }
+    LJ_D void finish(int) { what = 2; }
+};
+
 // ---- stage: generate (path_tracing.h:9-14, render.cpp:88-93 loop head) ----
+// The next sample of a slot: false when the slot has none left (or lies outside the film under a tile partition).
+LJ_D bool generate_slot(const DScene &sc, const WfPool &wp, int slot, int s_end, Ray &ray) {
+    ThrRec tr = wp.thr[slot];
+    int s = tr.sample + wp.map.K;
+    int pix, x, y;
+    const bool on_film = slot_pixel(wp.map, slot, pix, x, y);
+    if (s >= s_end || !on_film) { wp.hit[slot].geom = -2; return false; }   // slot exhausted: never traced again (see k_wf_shade, slot order)
+    int w = sc.camera.width, h = sc.camera.height;
+    Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)wp.map.npix_total + (unsigned long long)pix);
+    double u_first = pcg_real(rng), u_second = pcg_real(rng);   // right-to-left argument evaluation, see lj_path.cuh
+    ray = sample_primary(sc.camera, mk2((x + u_second) / w, (y + u_first) / h));
+    RayDiff rd = init_ray_differential(w, h);
+    RayRec rr; rr.ox = ray.org.x; rr.oy = ray.org.y; rr.oz = ray.org.z; rr.spread = rd.spread;
+    rr.dx = ray.dir.x; rr.dy = ray.dir.y; rr.dz = ray.dir.z; rr.eta_scale = 1;
+    tr.tx = tr.ty = tr.tz = 1; tr.p2 = 0; tr.fx = tr.fy = tr.fz = 0; tr.nv = 2; tr.sample = s;
+    RadRec ra; ra.rx = ra.ry = ra.rz = 0; ra.rng = rng.state;
+    wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
+    return true;
+}
+
 // Counter discipline of an iteration (all kernels of one render run in stream order, so a kernel may zero any counter
 // that neither it nor an earlier unfinished kernel uses): generate zeroes what the previous iteration's shade / shadow /
 // finish stages consumed, extend zeroes the regeneration queue generate has just drained, miss (launched before the
@@ -44,23 +93,9 @@ __global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n
         if (q == 0) { wp.counts[W_EXT] = 0; wp.counts[W_SHADOW] = 0; }
     }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_regen; i += gridDim.x * blockDim.x) {
-        int slot = wp.q_regen[i];
-        ThrRec tr = wp.thr[slot];
-        int s = tr.sample + wp.map.K;
-        int pix, x, y;
-        const bool on_film = slot_pixel(wp.map, slot, pix, x, y);
-        if (s >= s_end || !on_film) { wp.hit[slot].geom = -2; continue; }   // slot exhausted: never traced again (see k_wf_shade, slot order)
-        int w = sc.camera.width, h = sc.camera.height;
-        Pcg32 rng = pcg_init((unsigned long long)s * (unsigned long long)wp.map.npix_total + (unsigned long long)pix);
-        double u_first = pcg_real(rng), u_second = pcg_real(rng);   // right-to-left argument evaluation, see lj_path.cuh
-        Ray ray = sample_primary(sc.camera, mk2((x + u_second) / w, (y + u_first) / h));
-        RayDiff rd = init_ray_differential(w, h);
-        RayRec rr; rr.ox = ray.org.x; rr.oy = ray.org.y; rr.oz = ray.org.z; rr.spread = rd.spread;
-        rr.dx = ray.dir.x; rr.dy = ray.dir.y; rr.dz = ray.dir.z; rr.eta_scale = 1;
-        tr.tx = tr.ty = tr.tz = 1; tr.p2 = 0; tr.fx = tr.fy = tr.fz = 0; tr.nv = 2; tr.sample = s;
-        RadRec ra; ra.rx = ra.ry = ra.rz = 0; ra.rng = rng.state;
-        wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
-        push_extend(wp, slot, ray);
+        const int slot = wp.q_regen[i];
+        Ray ray;
+        if (generate_slot(sc, wp, slot, s_end, ray)) push_extend(wp, slot, ray);
     }
 }
 
@@ -92,8 +127,8 @@ namespace {
 // One bounce of path_tracing.h's loop body (:96-232) at a fresh vertex: NEE (shadow record),
 // BSDF sampling (next extension ray + the f / p2 the next stage needs).  Returns false when the
 // path ends here.  KIND is the compile-time material kind of the queue being processed.
-template <int KIND>
-LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const PathVertex &vertex, d3 dir_view,
+template <int KIND, typename Sink>
+LJ_D bool bounce_at_vertex(const DScene &sc, Sink &out, int slot, const PathVertex &vertex, d3 dir_view,
                            Pcg32 &rng, d3 throughput, RayRec &rr, ThrRec &tr, bool &pushed_shadow) {
     const unsigned grp = __activemask();     // lanes whose path is alive; see `together` in k_wf_shade
     MatParams mat = load_mat_params(sc, vertex);
@@ -128,10 +163,7 @@ LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const P
             C1 = C1 / p1;
             d3 contrib = throughput * C1 * w1;
             if (contrib.x != 0 || contrib.y != 0 || contrib.z != 0) {
-                ShadowRec s;
-                s.ray = to_rayf(make_ray(vertex.position, dir_light, eps, tfar));
-                s.cx = contrib.x; s.cy = contrib.y; s.cz = contrib.z; s.slot = slot; s._pad = 0;
-                wp.shadow[queue_push_uniform(&wp.counts[Q_SHADOW])] = s;
+                out.shadow(slot, to_rayf(make_ray(vertex.position, dir_light, eps, tfar)), contrib);
                 pushed_shadow = true;
             }
         }
@@ -163,8 +195,8 @@ LJ_D bool bounce_at_vertex(const DScene &sc, const WfPool &wp, int slot, const P
 #endif
 // One path vertex: finish the previous bounce with the new hit (emission + MIS, Russian roulette), then NEE + BSDF
 // sampling at the new vertex (path_tracing.h:58-61, :96-322).  Called by the lanes of a warp whose slot has a hit.
-template <int KIND>
-LJ_D void shade_slot(const DScene &sc, const WfPool &wp, const int slot, const HitRec &hr) {
+template <int KIND, typename Sink>
+LJ_D void shade_slot(const DScene &sc, const WfPool &wp, Sink &out, const int slot, const HitRec &hr) {
     // lanes that entered this iteration together; __syncwarp(together) below forces them to
     // reconverge after short divergent blocks (the compiler otherwise runs the long common
     // tail once per diverged group: 1.7x the instructions, seen in profiles/r01c)
@@ -214,20 +246,20 @@ LJ_D void shade_slot(const DScene &sc, const WfPool &wp, const int slot, const H
     const int max_depth = sc.options.max_depth;
     if (alive && !(max_depth == -1 || tr.nv <= max_depth + 1)) alive = false;
     bool pushed_shadow = false;
-    if (alive) alive = bounce_at_vertex<KIND>(sc, wp, slot, vertex, -ray.dir, rng, throughput, rr, tr, pushed_shadow);
+    if (alive) alive = bounce_at_vertex<KIND>(sc, out, slot, vertex, -ray.dir, rng, throughput, rr, tr, pushed_shadow);
     if (!alive) {
-        if (!pushed_shadow) { terminate_path(wp, slot, tr.sample, radiance); return; }
+        if (!pushed_shadow) { out.terminate(slot, tr.sample, radiance); return; }
         // the path ends here but its last NEE term is still in the shadow queue: park the
         // radiance and let the finish stage (after the shadow stage) do the accumulation
         ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
         wp.rad[slot] = ra;
-        wp.q_finish[queue_push_uniform(&wp.counts[Q_FINISH])] = slot;
+        out.finish(slot);
         return;
     }
     tr.tx = throughput.x; tr.ty = throughput.y; tr.tz = throughput.z;
     ra.rx = radiance.x; ra.ry = radiance.y; ra.rz = radiance.z; ra.rng = rng.state;
     wp.ray[slot] = rr; wp.thr[slot] = tr; wp.rad[slot] = ra;
-    push_extend(wp, slot, make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), sc.eps, INFINITY));
+    out.extend(slot, make_ray(mk3(rr.ox, rr.oy, rr.oz), mk3(rr.dx, rr.dy, rr.dz), sc.eps, INFINITY));
 }
 
 // Two ways to walk the work.  Queue order (SLOTS = false): the slots the extend stage put into this kind's queue.
@@ -244,42 +276,108 @@ __global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc
         const int i = base + lane;
         int slot = -1; HitRec hr; hr.geom = -1;
         if (i < n) { slot = SLOTS ? i : queue[i]; hr = wp.hit[slot]; }
-        if (hr.geom >= 0) shade_slot<KIND>(sc, wp, slot, hr);
+        if (hr.geom >= 0) { QueueSink out(wp); shade_slot<KIND>(sc, wp, out, slot, hr); }
         __syncwarp();       // the warp walks the range in lockstep: lanes without work wait here
     }
 }
 
 // ---- stage: miss (path_tracing.h:17-28 and :283-307) ----
+template <typename Sink>
+LJ_D void miss_slot(const DScene &sc, const WfPool &wp, Sink &out, int slot) {
+    RayRec rr = wp.ray[slot];
+    ThrRec tr = wp.thr[slot];
+    RadRec ra = wp.rad[slot];
+    d3 radiance = mk3(ra.rx, ra.ry, ra.rz);
+    if (sc.envmap_light_id != -1) {
+        const lj_light &env = sc.lights[sc.envmap_light_id];
+        d3 dir = mk3(rr.dx, rr.dy, rr.dz);
+        PointAndNormal dummy; dummy.position = mk3(0.0); dummy.normal = mk3(0.0);
+        d3 L = light_emission(sc, env, -dir, rr.spread, dummy);
+        if (tr.nv == 2) {
+            radiance = L;
+        } else {
+            d3 throughput = mk3(tr.tx, tr.ty, tr.tz), f = mk3(tr.fx, tr.fy, tr.fz);
+            double G = 1;
+            double p2 = tr.p2 * G;
+            d3 C2 = G * f * L;
+            PointAndNormal lp; lp.position = mk3(0.0); lp.normal = -dir;
+            double p1 = __ldg(sc.light_pmf + sc.envmap_light_id) * pdf_point_on_light(sc, env, lp, mk3(rr.ox, rr.oy, rr.oz));
+            double w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
+            C2 = C2 / p2;
+            radiance += throughput * C2 * w2;
+        }
+    }
+    out.terminate(slot, tr.sample, radiance);
+}
 __global__ void __launch_bounds__(128) k_wf_miss(DScene sc, WfPool wp, int n_upper) {
     int n = min(n_upper, wp.counts[Q_MISS]);
     if (blockIdx.x == 0 && threadIdx.x == 0) wp.counts[Q_EXT] = 0;      // drained by the extend stage; the shade kernels refill it
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
-        int slot = wp.q_miss[i];
-        RayRec rr = wp.ray[slot];
-        ThrRec tr = wp.thr[slot];
-        RadRec ra = wp.rad[slot];
-        d3 radiance = mk3(ra.rx, ra.ry, ra.rz);
-        if (sc.envmap_light_id != -1) {
-            const lj_light &env = sc.lights[sc.envmap_light_id];
-            d3 dir = mk3(rr.dx, rr.dy, rr.dz);
-            PointAndNormal dummy; dummy.position = mk3(0.0); dummy.normal = mk3(0.0);
-            d3 L = light_emission(sc, env, -dir, rr.spread, dummy);
-            if (tr.nv == 2) {
-                radiance = L;
-            } else {
-                d3 throughput = mk3(tr.tx, tr.ty, tr.tz), f = mk3(tr.fx, tr.fy, tr.fz);
-                double G = 1;
-                double p2 = tr.p2 * G;
-                d3 C2 = G * f * L;
-                PointAndNormal lp; lp.position = mk3(0.0); lp.normal = -dir;
-                double p1 = __ldg(sc.light_pmf + sc.envmap_light_id) * pdf_point_on_light(sc, env, lp, mk3(rr.ox, rr.oy, rr.oz));
-                double w2 = (p2 * p2) / (p1 * p1 + p2 * p2);
-                C2 = C2 / p2;
-                radiance += throughput * C2 * w2;
-            }
-        }
-        terminate_path(wp, slot, tr.sample, radiance);
+        QueueSink out(wp);
+        miss_slot(sc, wp, out, wp.q_miss[i]);
     }
+}
+
+// ---- tail: every remaining path to its end, one lane each ----
+// Once few paths are left, an iteration costs its launch and latency floor (six launches, ~0.17 ms on sponza) however
+// few rays it carries, and a render's last 30-odd iterations carry almost none: an 8-spp sponza render spent 5.5 of
+// 25.7 ms there, which is also what limits fixed-work multi-GPU scaling at low sample counts.  This kernel takes over
+// when the live count falls below a threshold: one lane per remaining slot runs trace -> miss / shade -> shadow ray ->
+// accumulate / regenerate in a loop until the slot has no samples left, with the SAME per-slot functions and slot
+// records as the stage kernels (their outputs go to the lane through LaneSink instead of the queues) and the same
+// traversal code run to completion per ray (trace_closest / trace_any), so results stay bit-identical.
+template <int KIND>
+__device__ __noinline__ void tail_shade(const DScene &sc, const WfPool &wp, LaneSink &out, int slot, const HitRec &hr) {
+    shade_slot<KIND>(sc, wp, out, slot, hr);
+}
+enum { T_PRIMARY = 0, T_EXTENSION = 1, T_SHADOW = 2 };     // ray counters of the tail kernel (u64, after the traversal counters)
+__global__ void __launch_bounds__(128, 2) k_wf_tail(DScene sc, WfPool wp, int s_end, unsigned long long *ray_counters) {
+    const int n_ext = wp.counts[Q_EXT], n_regen = wp.counts[Q_REGEN];
+    const int n = n_ext + n_regen;
+    unsigned c_primary = 0, c_extension = 0, c_shadow = 0;
+    for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
+        int slot; bool have_ray, primary = false; RayF ray;
+        if (i < n_ext) { slot = wp.ext_slot[i]; ray = wp.ext_ray[i].ray; have_ray = true; }
+        else { slot = wp.q_regen[i - n_ext]; have_ray = false; }
+        while (true) {
+            if (!have_ray) {
+                Ray r;
+                if (!generate_slot(sc, wp, slot, s_end, r)) break;
+                ray = to_rayf(r); primary = true;
+            }
+            Hit h;
+            const bool hit = trace_closest(sc, ray, &h);
+            if (primary) c_primary++; else c_extension++;
+            primary = false;
+            LaneSink out(wp);
+            if (!hit) { miss_slot(sc, wp, out, slot); have_ray = false; continue; }
+            HitRec hr; hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
+            switch (sc.materials[sc.shapes[h.geom].material_id].kind) {
+                case 0: tail_shade<0>(sc, wp, out, slot, hr); break;
+                case 1: tail_shade<1>(sc, wp, out, slot, hr); break;
+                case 2: tail_shade<2>(sc, wp, out, slot, hr); break;
+                case 3: tail_shade<3>(sc, wp, out, slot, hr); break;
+                case 4: tail_shade<4>(sc, wp, out, slot, hr); break;
+                case 5: tail_shade<5>(sc, wp, out, slot, hr); break;
+                case 6: tail_shade<6>(sc, wp, out, slot, hr); break;
+                case 7: tail_shade<7>(sc, wp, out, slot, hr); break;
+                default: tail_shade<8>(sc, wp, out, slot, hr); break;
+            }
+            if (out.has_shadow) {                               // k_wf_shadow: the NEE term counts unless the ray is blocked
+                c_shadow++;
+                if (!trace_any(sc, out.shadow_ray)) { RadRec *ra = &wp.rad[slot]; ra->rx += out.cx; ra->ry += out.cy; ra->rz += out.cz; }
+            }
+            if (out.what == 2) {                                // k_wf_finish
+                const RadRec ra = wp.rad[slot];
+                out.terminate(slot, wp.thr[slot].sample, mk3(ra.rx, ra.ry, ra.rz));
+                have_ray = false;
+            } else if (out.what == 1) { ray = out.next; have_ray = true; }
+            else have_ray = false;
+        }
+    }
+    if (c_primary) atomicAdd(&ray_counters[T_PRIMARY], (unsigned long long)c_primary);
+    if (c_extension) atomicAdd(&ray_counters[T_EXTENSION], (unsigned long long)c_extension);
+    if (c_shadow) atomicAdd(&ray_counters[T_SHADOW], (unsigned long long)c_shadow);
 }
 
 template <int KIND>
@@ -376,7 +474,62 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     auto grid_for = [](int n, int cap) { int g = (n + 127) / 128; return g < 1 ? 1 : (g > cap ? cap : g); };
     bool finished = false;
     int loop_rc = LJ_OK;
+    // retire what has completed (reads the counters an iteration left in the ring); blocks only when the host is as far
+    // ahead as it may go -- or, with `drain`, until nothing is in flight
+    auto retire = [&](bool drain) {
+        while (retired < launched) {
+            const int rs = (int)(retired % depth);
+
+            // how far the host runs ahead: one speculative iteration while iterations are large (it hides the read-back
+            // and costs at most one empty iteration at the end), the full ring once they are small and launch-bound
+            const unsigned long long ahead = (n_ext + n_regen) >= (1 << 19) ? (depth < 2 ? depth : 2) : depth;
+            if (!drain && launched - retired < ahead && cudaEventQuery(done[rs]) == cudaErrorNotReady) break;
+            const cudaError_t ce = cudaEventSynchronize(done[rs]);
+            if (ce != cudaSuccess) { lj_set_error("wavefront iteration failed: %s", cudaGetErrorString(ce)); loop_rc = LJ_ECUDA; finished = true; break; }
+            const int *h_counts = h_ring + rs * Q_COUNT;
+            int traced = h_counts[Q_MISS];
+            for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) traced += h_counts[Q_KIND0 + k];
+            // rays traced this iteration = hits + misses; all but the n_ext carried over are primaries
+            const int prim_now = traced - n_ext > 0 ? traced - n_ext : 0;
+            rays_primary += prim_now; rays_ext += traced - prim_now;
+            rays_shadow += h_counts[Q_SHADOW];
+            float ms_g = 0, ms_e = 0, ms_s = 0, ms_h = 0;
+            if (stage_timing) {
+                cudaEventElapsedTime(&ms_g, ev[rs][0], ev[rs][1]); cudaEventElapsedTime(&ms_e, ev[rs][1], ev[rs][2]);
+                cudaEventElapsedTime(&ms_s, ev[rs][2], ev[rs][3]); cudaEventElapsedTime(&ms_h, ev[rs][3], ev[rs][4]);
+                st->generate_ms += ms_g; st->extend_ms += ms_e; st->shade_ms += ms_s; st->shadow_ms += ms_h;
+            }
+            if (trace_iters)
+                fprintf(stderr, "[wf] iter %llu: traced %d (regen %d) shadow %d -> next ext %d regen %d | extend %.3f shade %.3f shadow %.3f ms\n",
+                        (unsigned long long)st->iterations, traced, n_regen, h_counts[Q_SHADOW], h_counts[Q_EXT], h_counts[Q_REGEN], ms_e, ms_s, ms_h);
+            n_regen = h_counts[Q_REGEN];
+            n_ext = h_counts[Q_EXT];
+            n_hits = traced - h_counts[Q_MISS];
+            st->iterations++;
+            retired++;
+            // (slots whose samples are used up sit in the regeneration queue once more: that iteration generates
+            //  nothing, extend zeroes the queue, and the counters come back empty)
+            if (n_ext == 0 && n_regen == 0) { finished = true; break; }
+        }
+    };
+    // Tail (k_wf_tail): once at most this many slots are live, one launch runs them all to completion
+    const int tail_threshold = env_int("LJ_WF_TAIL", 32768);
+    unsigned long long *tail_rays = (unsigned long long *)(wp.counts + 40);      // 3 x u64, zeroed with the counters
     while (!finished) {
+        if (tail_threshold > 0 && launched > 0 && n_ext + n_regen <= tail_threshold) {
+            retire(true);                               // exact sizes, nothing in flight
+            if (finished) break;
+            const int live_now = n_ext + n_regen;
+            k_wf_tail<<<grid_for(live_now, shade_grid_cap), 128>>>(d, wp, rl.s_end, tail_rays);
+            unsigned long long h_tail[3] = {0, 0, 0};
+            const cudaError_t ce = cudaMemcpy(h_tail, tail_rays, sizeof h_tail, cudaMemcpyDeviceToHost);
+            if (ce != cudaSuccess) { lj_set_error("wavefront tail failed: %s", cudaGetErrorString(ce)); loop_rc = LJ_ECUDA; break; }
+            rays_primary += h_tail[T_PRIMARY]; rays_ext += h_tail[T_EXTENSION]; rays_shadow += h_tail[T_SHADOW];
+            if (trace_iters) fprintf(stderr, "[wf] tail: %d live slots -> %llu + %llu + %llu rays\n", live_now, h_tail[0], h_tail[1], h_tail[2]);
+            launches++; st->iterations++;
+            finished = true;
+            break;
+        }
         // Slots only ever leave the pool (exhausted ones at the generate stage), so the live count of the last retired
         // iteration bounds every queue of every later iteration: grids are sized from it even while iterations are in
         // flight (all stage kernels are grid-stride / work-counter loops clamped to the device counts, so a bound that
@@ -413,42 +566,9 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         launches += 5;
         for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
         launched++;
-        // retire what has completed; block only when the ring is full
-        while (retired < launched) {
-            const int rs = (int)(retired % depth);
-            // how far the host runs ahead: one speculative iteration while iterations are large (it hides the read-back
-            // and costs at most one empty iteration at the end), the full ring once they are small and launch-bound
-            const unsigned long long ahead = (n_ext + n_regen) >= (1 << 19) ? (depth < 2 ? depth : 2) : depth;
-            if (launched - retired < ahead && cudaEventQuery(done[rs]) == cudaErrorNotReady) break;
-            const cudaError_t ce = cudaEventSynchronize(done[rs]);
-            if (ce != cudaSuccess) { lj_set_error("wavefront iteration failed: %s", cudaGetErrorString(ce)); loop_rc = LJ_ECUDA; finished = true; break; }
-            const int *h_counts = h_ring + rs * Q_COUNT;
-            int traced = h_counts[Q_MISS];
-            for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) traced += h_counts[Q_KIND0 + k];
-            // rays traced this iteration = hits + misses; all but the n_ext carried over are primaries
-            const int prim_now = traced - n_ext > 0 ? traced - n_ext : 0;
-            rays_primary += prim_now; rays_ext += traced - prim_now;
-            rays_shadow += h_counts[Q_SHADOW];
-            float ms_g = 0, ms_e = 0, ms_s = 0, ms_h = 0;
-            if (stage_timing) {
-                cudaEventElapsedTime(&ms_g, ev[rs][0], ev[rs][1]); cudaEventElapsedTime(&ms_e, ev[rs][1], ev[rs][2]);
-                cudaEventElapsedTime(&ms_s, ev[rs][2], ev[rs][3]); cudaEventElapsedTime(&ms_h, ev[rs][3], ev[rs][4]);
-                st->generate_ms += ms_g; st->extend_ms += ms_e; st->shade_ms += ms_s; st->shadow_ms += ms_h;
-            }
-            if (trace_iters)
-                fprintf(stderr, "[wf] iter %llu: traced %d (regen %d) shadow %d -> next ext %d regen %d | extend %.3f shade %.3f shadow %.3f ms\n",
-                        (unsigned long long)st->iterations, traced, n_regen, h_counts[Q_SHADOW], h_counts[Q_EXT], h_counts[Q_REGEN], ms_e, ms_s, ms_h);
-            n_regen = h_counts[Q_REGEN];
-            n_ext = h_counts[Q_EXT];
-            n_hits = traced - h_counts[Q_MISS];
-            st->iterations++;
-            retired++;
-            // (slots whose samples are used up sit in the regeneration queue once more: that iteration generates
-            //  nothing, extend zeroes the queue, and the counters come back empty)
-            if (n_ext == 0 && n_regen == 0) { finished = true; break; }
-        }
+        retire(false);
     }
-    cudaStreamSynchronize(0);           // drains the (empty) iterations still in flight before the ring is freed
+    cudaStreamSynchronize(0);           // drains the (empty) iterations still in flight
     cleanup();
     if (loop_rc != LJ_OK) return loop_rc;
     k_slot_sum<<<(unsigned)(((long long)map.npix_local * 3 + 255) / 256), 256>>>(map, wp.accum, dev_sum);
