@@ -2,6 +2,7 @@
 # Round-2 GPU visit: whole -m gpu suite, smoke, bench (+ reference arm), scenes table, then (each only after its own
 # command exited 0 without ncu) the ncu launch list of the bench command and --set full captures of the stage kernels.
 set -u
+TAG=${1:-r02}
 mkdir -p gpurun_out
 nvidia-smi --query-gpu=name,clocks.max.sm,clocks.max.mem --format=csv > gpurun_out/gpu.txt 2>&1
 timeout 1500 python -m pytest tests -m gpu -x -q -s > gpurun_out/pytest_gpu.log 2>&1; echo "pytest rc=$?" | tee -a gpurun_out/pytest_gpu.log
@@ -25,8 +26,8 @@ if [ $rc -eq 0 ]; then
       python tools/sweep_pool.py hetvol 8 8388608 > gpurun_out/ncu_full_track.log 2>&1; echo "ncu track rc=$?"
 fi
 # the reports are too big to travel (gpurun_out is capped at 64 MiB): summarise them here, keep only the summaries
-mkdir -p gpurun_out/profiles_r02
-python tools/summarize_profiles.py r02 gpurun_out gpurun_out/profiles_r02 > gpurun_out/summarize.log 2>&1; echo "summarize rc=$?"
+mkdir -p gpurun_out/profiles_$TAG
+python tools/summarize_profiles.py $TAG gpurun_out gpurun_out/profiles_$TAG > gpurun_out/summarize.log 2>&1; echo "summarize rc=$?"
 for k in extend shade; do ncu -i gpurun_out/${k}_full.ncu-rep --page source --csv > gpurun_out/${k}_source.csv 2>/dev/null; gzip -f gpurun_out/${k}_source.csv; done
 rm -f gpurun_out/*.ncu-rep
 du -sh gpurun_out
