@@ -419,10 +419,13 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     if (!d.bvh8) return lj_render_megakernel(s, rl, dev_sum, st);   // LJ_BVH=2 validation mode: binary tree only
     const long long npix = (long long)rl.width * rl.height;
     const int nsamp = rl.s_end - rl.s_begin;
-    // pool sizing: K sample lanes per owned pixel, ~12 Mi paths in flight unless the caller says otherwise (K is rounded
-    // down to a power of two, see SlotMap; sweep 2..16 Mi in profiles/r01_experiments.md: fewer, larger iterations;
-    // sponza is flat from 4 Mi, matpreview gains 13 % up to 16 Mi)
-    const long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (12LL << 20);
+    // pool sizing: K sample lanes per owned pixel (a power of two, see SlotMap).  Default 32 Mi slots (~15 GB of the context's
+    // arena): with shade in slot order and the tail kernel, fewer and larger iterations win on every scene measured (sponza
+    // 64 spp 166.5 / 161.2 / 156.4 / 152.1 ms at 4 / 8 / 16 / 32 Mi; matpreview 156.4 / 132.5 / 120.5 / 112.8; veach_mi 23.7 ms at
+    // 4 Mi, 19.8 at 32 Mi) except with the full Disney BSDF, whose shade kernel spills 1.4 kB per thread and wants its slot
+    // records near L2 (disney_bsdf 131-133 ms at 2-4 Mi, 154 at 16 Mi): 4 Mi there.  profiles/r02_experiments.md.
+    const long long dflt_slots = s->kind_present[LJ_MAT_DISNEY_BSDF] ? (4LL << 20) : (32LL << 20);
+    const long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : dflt_slots;
     const SlotMap map = lj_make_slot_map(rl.width, rl.height, rl.s_begin, rl.s_end, rl.p.tile_rank, rl.p.tile_world, target);
     if ((long long)map.npix_local * map.K > 0x7fffffffLL / 4) { lj_set_error("wavefront: pool too large"); return LJ_EINVAL; }
     WfPool wp;
