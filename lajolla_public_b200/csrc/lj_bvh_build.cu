@@ -618,6 +618,11 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     unsigned long long *keys = nullptr, *keys2 = nullptr;
     int *vals = nullptr, *vals2 = nullptr, *left = nullptr, *right = nullptr, *par_i = nullptr, *par_l = nullptr, *flags = nullptr, *count = nullptr;
     void *tmp = nullptr;
+    auto free_temps = [&]() {
+        lj_free(ref_prim);
+        lj_free(prim_lo); lj_free(prim_hi); lj_free(bounds); lj_free(keys); lj_free(keys2); lj_free(vals); lj_free(vals2);
+        lj_free(left); lj_free(right); lj_free(par_i); lj_free(par_l); lj_free(flags); lj_free(node_lo); lj_free(node_hi); lj_free(tmp); lj_free(count);
+    };
     CK(lj_malloc(&keys, 8 * (size_t)n)); CK(lj_malloc(&keys2, 8 * (size_t)n));
     CK(lj_malloc(&vals, 4 * (size_t)n)); CK(lj_malloc(&vals2, 4 * (size_t)n));
     k_morton<<<G, B>>>(n, prim_lo, prim_hi, bounds, keys, vals);
@@ -648,7 +653,7 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
             k_lbvh_counts<<<G, B>>>(n, left, right, count);
             out.bvh2_root = 0;
         } else {
-            if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, &out.bvh2_root, err) != 0) return -1;
+            if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, &out.bvh2_root, err) != 0) { free_temps(); return -1; }
         }
         pt.mark("PLOC");
         CK(lj_malloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
@@ -661,9 +666,7 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     // the 8-wide collapse consumes the binary tree (lj_bvh8_build.cu)
     int rc = lj_bvh8_collapse(n, out.bvh2_root, out.tri_verts, left, right, count, node_lo, node_hi, vals2, prim_lo, prim_hi, out, err);
     pt.mark("8-wide collapse");
-    lj_free(ref_prim);
-    lj_free(prim_lo); lj_free(prim_hi); lj_free(bounds); lj_free(keys); lj_free(keys2); lj_free(vals); lj_free(vals2);
-    lj_free(left); lj_free(right); lj_free(par_i); lj_free(par_l); lj_free(flags); lj_free(node_lo); lj_free(node_hi); lj_free(tmp); lj_free(count);
+    free_temps();
     return rc;
 }
 

@@ -650,8 +650,6 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     const bool counting = (rl.p.flags & 1) != 0;
     const bool stage_timing = (rl.p.flags & 2) != 0;
     unsigned long long *trav = (unsigned long long *)(vp.counts + 32);
-    cudaEvent_t ev[4];
-    if (stage_timing) for (auto &e : ev) cudaEventCreate(&e);
 
     LJ_CUDA(cudaMemsetAsync(vp.counts, 0, 64 * sizeof(int)));
     LJ_CUDA(cudaMemsetAsync(vp.accum, 0, (size_t)map.K0 * map.npix_local * 3 * sizeof(double)));
@@ -667,6 +665,7 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     if ((rc = lj_ctx_ring(s->ctx)) != LJ_OK) return rc;
     int *h_ring = s->ctx->h_ring;
     cudaEvent_t *done = s->ctx->ring_done;
+    cudaEvent_t *ev = s->ctx->ring_ev[0];           // stage timing runs with depth 1: ring slot 0's timing events
     int n_regen = capacity, n_ext = 0, n_cont = 0;  // sizes after the last retired iteration (n_cont: suspended segments)
     unsigned long long launches = 2, rays_primary = 0, rays_ext = 0;
     unsigned long long launched = 0, retired = 0;
@@ -754,7 +753,6 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         st->nodes_visited = h_trav[0]; st->prims_tested = h_trav[1];
     }
     launches++;
-    if (stage_timing) for (auto &e : ev) cudaEventDestroy(e);
     st->kernel_launches += launches;
     st->rays_primary += rays_primary; st->rays_extension += rays_ext;
     st->samples = (uint64_t)npix * (uint64_t)nsamp;

@@ -124,10 +124,12 @@ static inline SlotMap lj_make_slot_map(int width, int height, int s_begin, int s
         m.npix_local = (int)m.npix_total;
     }
     const int nsamp = s_end - s_begin;
-    // K0 from the film and the sample count only (never from the partition or the pool size)
-    long long by_mem = (32LL << 20) / (m.npix_total > 0 ? m.npix_total : 1);
+    // K0 from the film and the sample count only (never from the partition or the pool size): up to 256 Mi accumulator
+    // cells (6 GB of f64 RGB) over the whole film, so that at high sample counts a tile share of the film can keep as many
+    // paths in flight as a sample-slice share (sponza, 1024 spp on 8 GPUs: K0 = 512 instead of 64)
+    long long by_mem = (256LL << 20) / (m.npix_total > 0 ? m.npix_total : 1);
     int k0 = lj_pow2_ceil(nsamp);
-    if (k0 > 64) k0 = 64;
+    if (k0 > 1024) k0 = 1024;
     if (k0 > lj_pow2_floor(by_mem < 1 ? 1 : by_mem)) k0 = lj_pow2_floor(by_mem < 1 ? 1 : by_mem);
     m.K0 = k0;
     long long want = target_slots / m.npix_local;

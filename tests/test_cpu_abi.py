@@ -64,6 +64,14 @@ def test_no_device_fails_loudly():
     with pytest.raises(LjError) as ei:
         LajollaGPU(0)
     assert "lj_init failed" in str(ei.value)
+    # the multi-device entry point fails the same way (and loads neither NCCL nor anything else on the way)
+    with pytest.raises(LjError) as ei:
+        LajollaGPU("all")
+    assert "lj_init_devices failed" in str(ei.value) and "no CUDA device" in str(ei.value)
+    from lajolla_public_b200 import load_library
+    assert load_library().lj_ctx_device_count(None) == 0
+    # and so does the allocation-free finalize: argument checks come first, no device is touched
+    assert load_library().lj_accum_finalize_static(None, None, 1, 1, 1, None) < 0
 
 
 def test_null_arguments_are_rejected():

@@ -110,3 +110,18 @@ def test_cli_uses_all_devices_byte_identical(tmp_path):
         print([l for l in r.stdout.splitlines() if "lajolla_b200" in l][-1])
         outs.append(open(out, "rb").read())
     assert outs[0] == outs[1]
+
+
+def test_init_devices_argument_errors():
+    """lj_init_devices refuses ordinals out of range and duplicates; one listed device gives a plain one-device context"""
+    import ctypes as C
+    from lajolla_public_b200 import LajollaGPU, LjError
+    with pytest.raises(LjError, match="out of range"):
+        LajollaGPU([0, 999])
+    with pytest.raises(LjError, match="listed twice"):
+        LajollaGPU([0, 0])
+    g = LajollaGPU([0])
+    try:
+        assert g.n_devices == 1
+    finally:
+        g.close()
