@@ -467,6 +467,8 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     int n_kinds = 0;
     for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) n_kinds += kind_present[k] ? 1 : 0;
     const bool slots_ok = n_kinds == 1 && !getenv("LJ_SHADE_QUEUE");
+    wp.single_kind = -1;
+    if (n_kinds == 1 && !getenv("LJ_NO_SINGLE_KIND")) for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) if (kind_present[k]) wp.single_kind = k;
     // slot order while at least this share of the pool's slots had a hit in the last iteration the host has seen (below it
     // the idle lanes of missed / exhausted slots cost more than the coalesced records save: open scenes such as cbox, renders
     // without regeneration, and the tail of every render)
@@ -516,7 +518,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         }
     };
     // Tail (k_wf_tail): once at most this many slots are live, one launch runs them all to completion
-    const int tail_threshold = env_int("LJ_WF_TAIL", 32768);
+    const int tail_threshold = counting ? 0 : env_int("LJ_WF_TAIL", 32768);     // (the counting pass keeps every ray in the counting kernels)
     unsigned long long *tail_rays = (unsigned long long *)(wp.counts + 40);      // 3 x u64, zeroed with the counters
     while (!finished) {
         if (tail_threshold > 0 && launched > 0 && n_ext + n_regen <= tail_threshold) {

@@ -21,6 +21,8 @@ struct WfPool {
     ShadowRec *shadow;
     int *q_regen, *q_miss, *q_finish, *q_kind[LJ_MAT_KIND_COUNT];
     int *counts;                // Q_COUNT live queue sizes
+    int single_kind;            // the scene's only material kind, or -1: the extend stage then classifies a hit without
+                                // chasing shapes[geom] -> materials[id].kind (two dependent loads with few lanes active)
 };
 
 enum { W_EXT = 24, W_SHADOW = 25 };     // work counters of the trace kernels inside wp.counts

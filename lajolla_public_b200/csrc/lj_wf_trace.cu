@@ -44,7 +44,7 @@ __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_extend(DScene s
             Hit h; HitRec hr; int q;
             if (tv.finish(sc, &h)) {
                 hr.t = h.t; hr.u = h.u; hr.v = h.v; hr.geom = h.geom; hr.prim = h.prim; hr.ngx = h.ngx; hr.ngy = h.ngy; hr.ngz = h.ngz;
-                q = Q_KIND0 + sc.materials[sc.shapes[h.geom].material_id].kind;
+                q = Q_KIND0 + (wp.single_kind >= 0 ? wp.single_kind : sc.materials[sc.shapes[h.geom].material_id].kind);
             } else {
                 hr.t = 0; hr.u = hr.v = 0; hr.geom = -1; hr.prim = -1; hr.ngx = hr.ngy = hr.ngz = 0;
                 q = Q_MISS;
