@@ -75,7 +75,7 @@ struct SlotMap {
     int K, K0, s_begin;
 };
 
-LJ_D bool slot_pixel(const SlotMap &m, int slot, int &pix, int &x, int &y) {
+LJ_HD bool slot_pixel(const SlotMap &m, int slot, int &pix, int &x, int &y) {
     const int pl = slot % m.npix_local;
     if (m.tile_world <= 0) { pix = pl; x = pl % m.width; y = pl / m.width; return true; }
     int tx, ty;
@@ -85,12 +85,12 @@ LJ_D bool slot_pixel(const SlotMap &m, int slot, int &pix, int &x, int &y) {
     pix = y * m.width + x;
     return x < m.width && y < m.height;
 }
-LJ_D int slot_pixel_index(const SlotMap &m, int slot) { int pix, x, y; slot_pixel(m, slot, pix, x, y); return pix; }
-LJ_D unsigned long long slot_stream(const SlotMap &m, int slot, int sample) {
+LJ_HD int slot_pixel_index(const SlotMap &m, int slot) { int pix, x, y; slot_pixel(m, slot, pix, x, y); return pix; }
+LJ_HD unsigned long long slot_stream(const SlotMap &m, int slot, int sample) {
     return (unsigned long long)sample * (unsigned long long)m.npix_total + (unsigned long long)slot_pixel_index(m, slot);
 }
 // the three doubles sample `sample` of the slot's pixel is accumulated into
-LJ_D size_t accum_offset(const SlotMap &m, int slot, int sample) {
+LJ_HD size_t accum_offset(const SlotMap &m, int slot, int sample) {
     const int j = (sample - m.s_begin) & (m.K0 - 1);
     return 3 * ((size_t)j * m.npix_local + (size_t)(slot % m.npix_local));
 }
