@@ -54,7 +54,11 @@ void lj_shutdown_single(lj_ctx *ctx) {
     if (ctx->wf_pool) lj_free(ctx->wf_pool);
     cudaDeviceSynchronize();
     if (ctx->ring_ready) {
-        for (int i = 0; i < LJ_RING_DEPTH; i++) { cudaEventDestroy(ctx->ring_done[i]); for (auto &e : ctx->ring_ev[i]) cudaEventDestroy(e); }
+        for (int i = 0; i < LJ_RING_DEPTH; i++) {
+            cudaEventDestroy(ctx->ring_done[i]); for (auto &e : ctx->ring_ev[i]) cudaEventDestroy(e);
+            cudaEventDestroy(ctx->ring_a[i]); cudaEventDestroy(ctx->ring_b[i]);
+        }
+        cudaStreamDestroy(ctx->stream_b);
         cudaFreeHost(ctx->h_ring);
     }
     cudaMemPool_t pool;
@@ -68,7 +72,10 @@ int lj_ctx_ring(lj_ctx *ctx) {
     for (int i = 0; i < LJ_RING_DEPTH; i++) {
         LJ_CUDA(cudaEventCreateWithFlags(&ctx->ring_done[i], cudaEventDisableTiming));
         for (auto &e : ctx->ring_ev[i]) LJ_CUDA(cudaEventCreate(&e));
+        LJ_CUDA(cudaEventCreateWithFlags(&ctx->ring_a[i], cudaEventDisableTiming));
+        LJ_CUDA(cudaEventCreateWithFlags(&ctx->ring_b[i], cudaEventDisableTiming));
     }
+    LJ_CUDA(cudaStreamCreateWithFlags(&ctx->stream_b, cudaStreamNonBlocking));
     ctx->ring_ready = true;
     return LJ_OK;
 }

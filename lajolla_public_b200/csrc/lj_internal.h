@@ -19,6 +19,10 @@ struct lj_ctx {
     int *h_ring;                       // LJ_RING_DEPTH x LJ_RING_INTS ints, pinned
     cudaEvent_t ring_done[8];          // no-timing events, one per ring slot
     cudaEvent_t ring_ev[8][5];         // timing events per ring slot (stage times, lj_render_params.flags bit1)
+    // second stream of the surface wavefront engine (shadow + finish of an iteration beside generate + extend of the next,
+    // lj_wavefront.cu) and the events that join the two per ring slot
+    cudaStream_t stream_b;
+    cudaEvent_t ring_a[8], ring_b[8];
     bool ring_ready;
     // multi-device contexts (lj_init_devices, lj_multi.cu): the per-device contexts, worker threads and NCCL
     // communicators; null for a one-device context.  `this` is then only the handle and mirrors device 0.

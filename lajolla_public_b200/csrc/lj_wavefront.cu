@@ -81,16 +81,17 @@ LJ_D bool generate_slot(const DScene &sc, const WfPool &wp, int slot, int s_end,
     return true;
 }
 
-// Counter discipline of an iteration (all kernels of one render run in stream order, so a kernel may zero any counter
-// that neither it nor an earlier unfinished kernel uses): generate zeroes what the previous iteration's shade / shadow /
-// finish stages consumed, extend zeroes the regeneration queue generate has just drained, miss (launched before the
-// shade kernels) zeroes the extension queue extend has just drained.  No host-side reset launches.
+// Counter discipline of an iteration (a kernel may zero any counter that neither it nor a kernel that can still be running
+// uses): generate zeroes the hit / miss queues the previous iteration's miss and shade stages consumed, extend zeroes the
+// regeneration queue generate has just drained, miss (launched after the shadow + finish stages of the previous iteration
+// have been joined, before the shade kernels) zeroes the extension queue extend has just drained and the shadow / finish
+// queues of the previous iteration.  No host-side reset launches.
 __global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n_upper, int s_end) {
     const int n_regen = min(n_upper, wp.counts[Q_REGEN]);
     if (blockIdx.x == 0 && threadIdx.x < Q_COUNT) {
         const int q = threadIdx.x;
-        if (q == Q_SHADOW || q == Q_FINISH || q == Q_MISS || q >= Q_KIND0) wp.counts[q] = 0;
-        if (q == 0) { wp.counts[W_EXT] = 0; wp.counts[W_SHADOW] = 0; }
+        if (q == Q_MISS || q >= Q_KIND0) wp.counts[q] = 0;
+        if (q == 0) wp.counts[W_EXT] = 0;
     }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n_regen; i += gridDim.x * blockDim.x) {
         const int slot = wp.q_regen[i];
@@ -100,12 +101,20 @@ __global__ void __launch_bounds__(128) k_wf_generate(DScene sc, WfPool wp, int n
 }
 
 // ---- stage: finish = accumulate paths whose last NEE term had to wait for the shadow stage ----
-__global__ void __launch_bounds__(128) k_wf_finish(WfPool wp, int n_upper) {
+// `no_regen`: no slot of this render has a further sample (K = samples per pixel), so a finished slot is marked exhausted here
+// instead of going through the regeneration queue -- which lets this stage run beside the next iteration's generate / extend.
+__global__ void __launch_bounds__(128) k_wf_finish(WfPool wp, int n_upper, int no_regen) {
     int n = min(n_upper, wp.counts[Q_FINISH]);
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         int slot = wp.q_finish[i];
         RadRec ra = wp.rad[slot];
-        terminate_path(wp, slot, wp.thr[slot].sample, mk3(ra.rx, ra.ry, ra.rz));
+        if (no_regen) {
+            LaneSink out(wp);
+            out.terminate(slot, wp.thr[slot].sample, mk3(ra.rx, ra.ry, ra.rz));
+            wp.hit[slot].geom = -2;
+        } else {
+            terminate_path(wp, slot, wp.thr[slot].sample, mk3(ra.rx, ra.ry, ra.rz));
+        }
     }
 }
 
@@ -311,7 +320,9 @@ LJ_D void miss_slot(const DScene &sc, const WfPool &wp, Sink &out, int slot) {
 }
 __global__ void __launch_bounds__(128) k_wf_miss(DScene sc, WfPool wp, int n_upper) {
     int n = min(n_upper, wp.counts[Q_MISS]);
-    if (blockIdx.x == 0 && threadIdx.x == 0) wp.counts[Q_EXT] = 0;      // drained by the extend stage; the shade kernels refill it
+    if (blockIdx.x == 0 && threadIdx.x == 0) {      // drained by the extend stage / by the previous iteration's shadow and finish stages; the shade kernels refill them
+        wp.counts[Q_EXT] = 0; wp.counts[Q_SHADOW] = 0; wp.counts[Q_FINISH] = 0; wp.counts[W_SHADOW] = 0;
+    }
     for (int i = blockIdx.x * blockDim.x + threadIdx.x; i < n; i += gridDim.x * blockDim.x) {
         QueueSink out(wp);
         miss_slot(sc, wp, out, wp.q_miss[i]);
@@ -457,6 +468,14 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     cudaEvent_t *done = s->ctx->ring_done;
     cudaEvent_t (*ev)[5] = s->ctx->ring_ev;
     auto cleanup = [&]() {};
+    // Shadow + finish of iteration i beside generate + extend of iteration i + 1 (second stream): possible when no slot can
+    // regenerate (K sample lanes = samples per pixel), because then nothing the finish stage produces is needed before the
+    // next shade stage -- a finished slot is marked exhausted on the spot.  The extend kernel leaves about a third of the
+    // issue slots idle and the shadow kernel's warps fit beside its 40 per SM.  LJ_WF_OVERLAP=0 turns it off.
+    const bool no_regen = map.K >= nsamp;
+    const bool overlap = no_regen && env_int("LJ_WF_OVERLAP", 1) != 0 && !trace_iters;
+    cudaStream_t sb = s->ctx->stream_b;
+    cudaEvent_t *ring_a = s->ctx->ring_a, *ring_b = s->ctx->ring_b;
 
     cudaMemsetAsync(wp.counts, 0, 64 * sizeof(int));
     cudaMemsetAsync(wp.accum, 0, (size_t)map.K0 * map.npix_local * 3 * sizeof(double));
@@ -514,17 +533,19 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
             retired++;
             // (slots whose samples are used up sit in the regeneration queue once more: that iteration generates
             //  nothing, extend zeroes the queue, and the counters come back empty)
-            if (n_ext == 0 && n_regen == 0) { finished = true; break; }
+            //  Without regeneration the slots in the regeneration queue are finished ones waiting to be marked exhausted.)
+            if (n_ext == 0 && (no_regen || n_regen == 0)) { finished = true; break; }
         }
     };
     // Tail (k_wf_tail): once at most this many slots are live, one launch runs them all to completion
     const int tail_threshold = counting ? 0 : env_int("LJ_WF_TAIL", 32768);     // (the counting pass keeps every ray in the counting kernels)
     unsigned long long *tail_rays = (unsigned long long *)(wp.counts + 40);      // 3 x u64, zeroed with the counters
     while (!finished) {
-        if (tail_threshold > 0 && launched > 0 && n_ext + n_regen <= tail_threshold) {
+        if (tail_threshold > 0 && retired > 0 && n_ext + (no_regen ? 0 : n_regen) <= tail_threshold) {     // (sizes are real once an iteration has been retired)
             retire(true);                               // exact sizes, nothing in flight
+            if (overlap && launched > 0) cudaStreamWaitEvent(0, ring_b[(launched - 1) % depth], 0);
             if (finished) break;
-            const int live_now = n_ext + n_regen;
+            const int live_now = n_ext + n_regen;          // (regeneration entries included: the tail kernel marks them exhausted)
             k_wf_tail<<<grid_for(live_now, shade_grid_cap), 128>>>(d, wp, rl.s_end, tail_rays);
             unsigned long long h_tail[3] = {0, 0, 0};
             const cudaError_t ce = cudaMemcpy(h_tail, tail_rays, sizeof h_tail, cudaMemcpyDeviceToHost);
@@ -541,7 +562,7 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         // is a few iterations stale costs nothing but a few idle blocks).
         const bool exact = launched == retired;          // nothing in flight: the sizes are the true ones
         const int live = n_ext + n_regen > capacity ? capacity : n_ext + n_regen;
-        const int regen_upper = exact ? n_regen : live;
+        const int regen_upper = (exact && !overlap) ? n_regen : live;
         const int upper = live;
         const int ring_slot = (int)(launched % depth);
         cudaEvent_t *e = ev[ring_slot];
@@ -552,6 +573,9 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         if (stage_timing) cudaEventRecord(e[2]);
         // slot order while most of the pool is live (the last sizes the host has seen), queue order in the tail
         const bool slot_order = slots_ok && (long long)n_hits * 100 >= (long long)capacity * slots_min_live_pct;
+        // the shadow + finish stages of the previous iteration (on the second stream when overlapped) are joined here: miss
+        // resets their queues, shade reads the radiance they updated
+        if (overlap && launched > 0) cudaStreamWaitEvent(0, ring_b[(launched - 1) % depth], 0);
         k_wf_miss<<<grid_for(upper, shade_grid_cap), 128>>>(d, wp, upper);
         if (kind_present[0]) launch_shade<0>(d, wp, upper, shade_grid_cap, slot_order);
         if (kind_present[1]) launch_shade<1>(d, wp, upper, shade_grid_cap, slot_order);
@@ -562,18 +586,32 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
         if (kind_present[6]) launch_shade<6>(d, wp, upper, shade_grid_cap, slot_order);
         if (kind_present[7]) launch_shade<7>(d, wp, upper, shade_grid_cap, slot_order);
         if (kind_present[8]) launch_shade<8>(d, wp, upper, shade_grid_cap, slot_order);
-        if (stage_timing) cudaEventRecord(e[3]);
-        lj_wf_launch_shadow(d, wp, upper, trav, tune_sh, counting, grid_for(upper, trace_grid_cap));
-        k_wf_finish<<<grid_for(upper, shade_grid_cap), 128>>>(wp, upper);
-        if (stage_timing) cudaEventRecord(e[4]);
-        cudaMemcpyAsync(h_ring + ring_slot * Q_COUNT, wp.counts, sizeof(int) * Q_COUNT, cudaMemcpyDeviceToHost);
-        cudaEventRecord(done[ring_slot]);
+        if (overlap) {
+            // every counter the host needs is final once the shade stage is done (the finish stage pushes nothing here)
+            cudaMemcpyAsync(h_ring + ring_slot * Q_COUNT, wp.counts, sizeof(int) * Q_COUNT, cudaMemcpyDeviceToHost);
+            cudaEventRecord(done[ring_slot]);
+            cudaEventRecord(ring_a[ring_slot]);
+            cudaStreamWaitEvent(sb, ring_a[ring_slot], 0);
+            if (stage_timing) cudaEventRecord(e[3], sb);
+            lj_wf_launch_shadow(d, wp, upper, trav, tune_sh, counting, grid_for(upper, trace_grid_cap), sb);
+            k_wf_finish<<<grid_for(upper, shade_grid_cap), 128, 0, sb>>>(wp, upper, 1);
+            if (stage_timing) cudaEventRecord(e[4], sb);
+            cudaEventRecord(ring_b[ring_slot], sb);
+        } else {
+            if (stage_timing) cudaEventRecord(e[3]);
+            lj_wf_launch_shadow(d, wp, upper, trav, tune_sh, counting, grid_for(upper, trace_grid_cap), 0);
+            k_wf_finish<<<grid_for(upper, shade_grid_cap), 128>>>(wp, upper, 0);
+            if (stage_timing) cudaEventRecord(e[4]);
+            cudaMemcpyAsync(h_ring + ring_slot * Q_COUNT, wp.counts, sizeof(int) * Q_COUNT, cudaMemcpyDeviceToHost);
+            cudaEventRecord(done[ring_slot]);
+        }
         launches += 5;
         for (int k = 0; k < LJ_MAT_KIND_COUNT; k++) launches += kind_present[k] ? 1 : 0;
         launched++;
         retire(false);
     }
     cudaStreamSynchronize(0);           // drains the (empty) iterations still in flight
+    if (overlap) cudaStreamSynchronize(sb);
     cleanup();
     if (loop_rc != LJ_OK) return loop_rc;
     k_slot_sum<<<(unsigned)(((long long)map.npix_local * 3 + 255) / 256), 256>>>(map, wp.accum, dev_sum);

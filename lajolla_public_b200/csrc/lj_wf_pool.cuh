@@ -29,4 +29,4 @@ enum { W_EXT = 24, W_SHADOW = 25 };     // work counters of the trace kernels in
 
 // extend = rtcIntersect1 + classification by material kind; shadow = rtcOccluded1 + NEE accumulation
 void lj_wf_launch_extend(const DScene &sc, const WfPool &wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune, bool counting, unsigned grid);
-void lj_wf_launch_shadow(const DScene &sc, const WfPool &wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune, bool counting, unsigned grid);
+void lj_wf_launch_shadow(const DScene &sc, const WfPool &wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune, bool counting, unsigned grid, cudaStream_t stream);

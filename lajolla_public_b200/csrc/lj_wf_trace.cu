@@ -141,7 +141,7 @@ void lj_wf_launch_extend(const DScene &sc, const WfPool &wp, int n_upper, unsign
     if (counting) k_wf_extend<true><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
     else k_wf_extend<false><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
 }
-void lj_wf_launch_shadow(const DScene &sc, const WfPool &wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune, bool counting, unsigned grid) {
-    if (counting) k_wf_shadow<true><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
-    else k_wf_shadow<false><<<grid, 128>>>(sc, wp, n_upper, trav_counters, tune);
+void lj_wf_launch_shadow(const DScene &sc, const WfPool &wp, int n_upper, unsigned long long *trav_counters, TraceTuning tune, bool counting, unsigned grid, cudaStream_t stream) {
+    if (counting) k_wf_shadow<true><<<grid, 128, 0, stream>>>(sc, wp, n_upper, trav_counters, tune);
+    else k_wf_shadow<false><<<grid, 128, 0, stream>>>(sc, wp, n_upper, trav_counters, tune);
 }
