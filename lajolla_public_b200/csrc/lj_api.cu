@@ -94,24 +94,32 @@ int lj_ctx_arena(lj_ctx *ctx, size_t bytes, void **out) {
 // All scene arrays go into ONE device allocation (sub-allocated at 256-byte boundaries) filled with
 // asynchronous copies: a scene is ~20 arrays, and a cudaMalloc + blocking copy per array cost more than
 // the transfer itself (sponza: 73 MB).
+// Arrays marked `late` (the texels: 66 of sponza's 73 MB) are not needed by the BVH build; they are copied on the context's
+// second stream so that the build kernels run while they are still in flight (from pinned host memory; a pageable source
+// is staged by the driver and simply takes its usual time).  `late_done` is recorded behind them.
 struct Uploader {
-    struct Item { const void *host; size_t bytes, offset; const void **dev; };
+    struct Item { const void *host; size_t bytes, offset; const void **dev; bool late; };
     std::vector<Item> items;
     size_t total = 0;
     template <typename T>
-    void add(const T *host, size_t count, const T **dev) {
-        Item it; it.host = host; it.bytes = sizeof(T) * count; it.offset = total; it.dev = (const void **)dev;
+    void add(const T *host, size_t count, const T **dev, bool late = false) {
+        Item it; it.host = host; it.bytes = sizeof(T) * count; it.offset = total; it.dev = (const void **)dev; it.late = late;
         total += (sizeof(T) * (count ? count : 1) + 255) & ~(size_t)255;
         items.push_back(it);
     }
-    int commit(lj_scene *s) {
+    int commit(lj_scene *s, cudaStream_t late_stream, cudaEvent_t late_done) {
         void *base = nullptr;
         LJ_CUDA(lj_malloc(&base, total ? total : 256));
         s->allocs.push_back(base);
+        LJ_CUDA(cudaEventRecord(late_done));                       // the allocation is ordered on this thread's stream
+        LJ_CUDA(cudaStreamWaitEvent(late_stream, late_done, 0));
         for (const Item &it : items) {
             *it.dev = (const char *)base + it.offset;
-            if (it.bytes) LJ_CUDA(cudaMemcpyAsync((char *)base + it.offset, it.host, it.bytes, cudaMemcpyHostToDevice));
+            if (it.bytes && !it.late) LJ_CUDA(cudaMemcpyAsync((char *)base + it.offset, it.host, it.bytes, cudaMemcpyHostToDevice));
         }
+        for (const Item &it : items)
+            if (it.bytes && it.late) LJ_CUDA(cudaMemcpyAsync((char *)base + it.offset, it.host, it.bytes, cudaMemcpyHostToDevice, late_stream));
+        LJ_CUDA(cudaEventRecord(late_done, late_stream));
         return LJ_OK;
     }
 };
@@ -274,7 +282,7 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
     up.add(grid_f32.data(), grid_f32.size(), &d.grid_f32);
     UP(textures, desc->num_textures) UP(images1, desc->num_images1) UP(images3, desc->num_images3)
     UP(positions, desc->num_positions * 3) UP(normals, desc->num_positions * 3) UP(uvs, desc->num_positions * 2)
-    UP(indices, desc->num_indices * 3) UP(texels, desc->num_texels) UP(tables, desc->num_tables) UP(grid_data, need_f64_grids ? desc->num_grid_data : 0)
+    UP(indices, desc->num_indices * 3) up.add(desc->texels, (size_t)desc->num_texels, &d.texels, true); UP(tables, desc->num_tables) UP(grid_data, need_f64_grids ? desc->num_grid_data : 0)
 #undef UP
 
     // primitive lists for the BVH builder
@@ -292,24 +300,12 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
     const int *d_tri_shape; const SpherePrim *d_spheres;
     up.add(tri_shape.data(), tri_shape.size(), &d_tri_shape);
     up.add(spheres.data(), spheres.size(), &d_spheres);
-    if ((rc = up.commit(s)) != LJ_OK) { cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc; }
+    if ((rc = lj_ctx_ring(ctx)) != LJ_OK) { cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc; }
+    cudaEvent_t late_done = ctx->ring_a[0];         // (no render is in flight during a scene create)
+    if ((rc = up.commit(s, ctx->stream_b, late_done)) != LJ_OK) { cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc; }
     d.light_pmf = d.tables + desc->light_pmf_offset;
     d.light_cdf = d.tables + desc->light_cdf_offset;
     cudaEventRecord(e1);
-    if (flags & LJ_SCENE_BUILD_TABLES) {
-        float tms = 0;
-        if ((rc = lj_scene_build_tables(s, desc, (flags & LJ_SCENE_POISON_DERIVED) != 0, &tms)) != LJ_OK) {
-            cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc;
-        }
-        s->build_stats.tables_build_ms = tms;
-        cudaEventRecord(e1);
-    }
-
-    if ((rc = lj_scene_build_shading_cache(s, desc, d_tri_shape)) != LJ_OK) {
-        cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc;
-    }
-    cudaEventRecord(e1);
-
     BvhBuildInput bi;
     bi.num_tris = (int)desc->num_indices; bi.num_spheres = (int)spheres.size();
     bi.positions = d.positions; bi.indices = d.indices; bi.tri_shape = d_tri_shape; bi.shapes = d.shapes; bi.spheres = d_spheres;
@@ -330,7 +326,24 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
         }
     }
     cudaEventRecord(e2);
-    cudaEventSynchronize(e2);
+    // the texels have been arriving on the second stream meanwhile; everything below reads them
+    cudaStreamWaitEvent(0, late_done, 0);
+    if (flags & LJ_SCENE_BUILD_TABLES) {
+        float tms = 0;
+        if ((rc = lj_scene_build_tables(s, desc, (flags & LJ_SCENE_POISON_DERIVED) != 0, &tms)) != LJ_OK) {
+            cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc;
+        }
+        s->build_stats.tables_build_ms = tms;
+    }
+
+    if ((rc = lj_scene_build_shading_cache(s, desc, d_tri_shape)) != LJ_OK) {
+        cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2); lj_scene_destroy_single(s); return rc;
+    }
+
+    cudaEvent_t e3; cudaEventCreate(&e3);
+    cudaEventRecord(e3);
+    cudaEventSynchronize(e3);
+
     d.num_tris = bi.num_tris; d.num_spheres = bi.num_spheres; d.num_prims = s->bvh.num_prims;
     d.tri_verts = s->bvh.tri_verts; d.spheres = d_spheres;
     d.bvh2 = s->bvh.bvh2; d.bvh2_root = s->bvh.bvh2_root;
@@ -340,8 +353,13 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
     if (const char *bv = getenv("LJ_BVH")) if (atoi(bv) == 2) d.bvh8 = nullptr;
     if (d.bvh8) d.tri_verts = s->bvh.tri_verts8;
     float ms = 0;
-    cudaEventElapsedTime(&ms, e0, e1); s->build_stats.upload_ms = ms - s->build_stats.tables_build_ms;
+    // upload = the arrays the build needs (e0..e1) + whatever of the texel copy, the table build and the shading caches was
+    // still to do when the BVH build finished (e2..e3)
+    float ms_tail = 0;
+    cudaEventElapsedTime(&ms, e0, e1); cudaEventElapsedTime(&ms_tail, e2, e3);
+    s->build_stats.upload_ms = ms + ms_tail - s->build_stats.tables_build_ms;
     cudaEventElapsedTime(&ms, e1, e2); s->build_stats.bvh_build_ms = ms;
+    cudaEventDestroy(e3);
     s->build_stats.bvh_nodes = s->bvh.bvh8 ? s->bvh.num_bvh8 : s->bvh.num_bvh2;
     s->build_stats.bvh_prims = s->bvh.num_prims;
     cudaEventDestroy(e0); cudaEventDestroy(e1); cudaEventDestroy(e2);
@@ -356,6 +374,7 @@ extern "C" void lj_scene_destroy(lj_scene *s) {
 void lj_scene_destroy_single(lj_scene *s) {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
+    if (s->ctx->ring_ready) cudaStreamSynchronize(s->ctx->stream_b);      // an upload of this scene may still be in flight there (failed create)
     for (void *p : s->allocs) lj_free(p);
     lj_bvh_free(s->bvh);
     delete s;
