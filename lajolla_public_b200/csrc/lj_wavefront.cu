@@ -473,7 +473,9 @@ int lj_render_wavefront(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj
     // next shade stage -- a finished slot is marked exhausted on the spot.  The extend kernel leaves about a third of the
     // issue slots idle and the shadow kernel's warps fit beside its 40 per SM.  LJ_WF_OVERLAP=0 turns it off.
     const bool no_regen = map.K >= nsamp;
-    const bool overlap = no_regen && env_int("LJ_WF_OVERLAP", 1) != 0 && !trace_iters;
+    // (not with per-stage timing, lj_render_params.flags bit1: a stage's CUDA-event interval is only that stage's time when the
+    //  stages run one after the other -- bench.py's roofline divides by the extend kernel's own duration)
+    const bool overlap = no_regen && env_int("LJ_WF_OVERLAP", 1) != 0 && !stage_timing;
     cudaStream_t sb = s->ctx->stream_b;
     cudaEvent_t *ring_a = s->ctx->ring_a, *ring_b = s->ctx->ring_b;
 
