@@ -7,6 +7,7 @@
 #include "lj_bvh_build.h"
 #include "lj_alloc.h"
 
+#include <cooperative_groups.h>
 #include <cfloat>
 #include <cstdio>
 #include <cstdlib>
@@ -29,14 +30,12 @@ __device__ __forceinline__ void child_box(int c, const float4 *node_lo, const fl
     lo[0] = l.x; lo[1] = l.y; lo[2] = l.z; hi[0] = h.x; hi[1] = h.y; hi[2] = h.z;
 }
 
-__global__ void k_collapse_level(const Work *items, int n_items, Work *items_out, int *n_out,
-                                 const int *left, const int *right, const float4 *node_lo, const float4 *node_hi,
-                                 const int *count, const int *sorted_prim,
-                                 const float4 *prim_lo, const float4 *prim_hi, const float4 *tri_verts,
-                                 Bvh8Node *nodes8, int *node_counter, float4 *tri_verts8, int *prim_counter, int n_prims_total, int MAX_LEAF, int open_leaves) {
-    int wi = blockIdx.x * blockDim.x + threadIdx.x;
-    if (wi >= n_items) return;
-    Work w = items[wi];
+// One work item = one 8-wide node: gathers up to 8 children of binary node w.node2, writes node w.node8, queues the inner children.
+__device__ void collapse_item(const Work w, Work *items_out, int *n_out,
+                              const int *left, const int *right, const float4 *node_lo, const float4 *node_hi,
+                              const int *count, const int *sorted_prim,
+                              const float4 *prim_lo, const float4 *prim_hi, const float4 *tri_verts,
+                              Bvh8Node *nodes8, int *node_counter, float4 *tri_verts8, int *prim_counter, int n_prims_total, int MAX_LEAF, int open_leaves) {
     int child[8]; int nchild;
     float plo[3], phi[3];
     if (w.node2 < 0) {            // degenerate tree: a single primitive
@@ -184,43 +183,101 @@ __global__ void k_collapse_level(const Work *items, int n_items, Work *items_out
     nodes8[w.node8] = nd;
 }
 
+struct CollapseArgs {
+    const int *left, *right; const float4 *node_lo, *node_hi; const int *count, *sorted_prim;
+    const float4 *prim_lo, *prim_hi, *tri_verts;
+    Bvh8Node *nodes8; float4 *tri_verts8; int n_prims_total, max_leaf, open_leaves;
+};
+// counters: [0] 8-wide nodes allocated, [1] primitive slots, [2..4] queue sizes of three consecutive levels (rotating), [5] levels
+
+// one level per launch (LJ_BVH8_COOP=0): the host reads the size of the next level back after each
+__global__ void k_collapse_level(const Work *items, int n_items, Work *items_out, int *n_out, int *counters, CollapseArgs a) {
+    int wi = blockIdx.x * blockDim.x + threadIdx.x;
+    if (wi >= n_items) return;
+    collapse_item(items[wi], items_out, n_out, a.left, a.right, a.node_lo, a.node_hi, a.count, a.sorted_prim, a.prim_lo, a.prim_hi, a.tri_verts,
+                  a.nodes8, counters, a.tri_verts8, counters + 1, a.n_prims_total, a.max_leaf, a.open_leaves);
+}
+__global__ void k_collapse_root(Work *q0, const int *d_root2, int n) {
+    Work root; root.node2 = (n >= 2) ? *d_root2 : ~0; root.node8 = 0;
+    q0[0] = root;
+}
+
+// every level in ONE cooperative launch (the default): a grid barrier between levels instead of a launch, a memset and a
+// blocking read-back.  The queue size of level L is counters[2 + L % 3]; level L fills the counter of L + 1 and zeroes
+// the one of L + 2 (last read before the previous barrier).
+__global__ void __launch_bounds__(64) k_collapse_all(Work *q0, Work *q1, int *counters, const int *d_root2, CollapseArgs a) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    const int gtid = blockIdx.x * blockDim.x + threadIdx.x, gsize = gridDim.x * blockDim.x;
+    int level = 0, n_items = 1;
+    while (n_items > 0 && level <= 128) {
+        const Work *items = (level & 1) ? q1 : q0;
+        Work *items_out = (level & 1) ? q0 : q1;
+        int *n_out = counters + 2 + (level + 1) % 3;
+        if (gtid == 0) counters[2 + (level + 2) % 3] = 0;
+        for (int wi = gtid; wi < n_items; wi += gsize) {
+            Work w;
+            if (level == 0) { w.node2 = (a.n_prims_total >= 2) ? *d_root2 : ~0; w.node8 = 0; } else w = items[wi];
+            collapse_item(w, items_out, n_out, a.left, a.right, a.node_lo, a.node_hi, a.count, a.sorted_prim, a.prim_lo, a.prim_hi, a.tri_verts,
+                          a.nodes8, counters, a.tri_verts8, counters + 1, a.n_prims_total, a.max_leaf, a.open_leaves);
+        }
+        grid.sync();
+        n_items = *(volatile int *)n_out;
+        level++;
+    }
+    if (gtid == 0) counters[5] = level;
+}
+
 } // namespace
 
-int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left, const int *right, const int *count,
+// d_root2 (device): root id of the binary tree (ignored when n < 2).  d_counters_out (device, 6 ints): the counters described
+// above, left for the caller to read back together with its own results: [0] nodes, [1] slots, [5] levels (> 128 = did not terminate).
+int lj_bvh8_collapse(int n, const int *d_root2, const float4 *tri_verts, const int *left, const int *right, const int *count,
                      const float4 *node_lo, const float4 *node_hi, const int *sorted_prim,
-                     const float4 *prim_lo, const float4 *prim_hi, BvhBuildOutput &out, char *err) {
+                     const float4 *prim_lo, const float4 *prim_hi, BvhBuildOutput &out, int *counters, char *err) {
     if (n <= 0) return 0;
-    int *counters = nullptr;
     Work *q0 = nullptr, *q1 = nullptr;
-    CK(lj_malloc(&counters, 4 * sizeof(int)));
     CK(lj_malloc(&q0, sizeof(Work) * (size_t)n)); CK(lj_malloc(&q1, sizeof(Work) * (size_t)n));
     CK(lj_malloc(&out.bvh8, sizeof(Bvh8Node) * (size_t)n));
     CK(lj_malloc(&out.tri_verts8, sizeof(float4) * 3 * (size_t)n));
-    int h_counters[4] = {1 /* nodes allocated: root */, 0 /* prims */, 0 /* out items */, 0};
-    CK(cudaMemcpy(counters, h_counters, sizeof h_counters, cudaMemcpyHostToDevice));
-    Work root; root.node2 = (n >= 2) ? root2 : ~0; root.node8 = 0;
-    CK(cudaMemcpy(q0, &root, sizeof root, cudaMemcpyHostToDevice));
-    int max_leaf = MAX_LEAF_CAP;      // LJ_MAX_LEAF: experiment knob (1..3)
-    if (const char *e = getenv("LJ_MAX_LEAF")) { int v = atoi(e); if (v >= 1 && v <= MAX_LEAF_CAP) max_leaf = v; }
-    int open_leaves = 1;              // LJ_OPEN_LEAVES=0: experiment knob
-    if (const char *e = getenv("LJ_OPEN_LEAVES")) open_leaves = atoi(e) != 0;
-    int n_items = 1;
-    int levels = 0;
-    while (n_items > 0) {
-        CK(cudaMemset(counters + 2, 0, sizeof(int)));
-        k_collapse_level<<<(n_items + 63) / 64, 64>>>(q0, n_items, q1, counters + 2, left, right, node_lo, node_hi,
-                                                       count, sorted_prim, prim_lo, prim_hi, tri_verts,
-                                                       out.bvh8, counters, out.tri_verts8, counters + 1, n, max_leaf, open_leaves);
-        CK(cudaGetLastError());
-        CK(cudaMemcpy(h_counters, counters, sizeof h_counters, cudaMemcpyDeviceToHost));
-        n_items = h_counters[2];
-        Work *t = q0; q0 = q1; q1 = t;
-        if (++levels > 128) { snprintf(err, 256, "bvh8 collapse did not terminate"); return -1; }
+    int h_counters[6] = {1 /* nodes allocated: root */, 0 /* prims */, 1, 0, 0, 0};
+    CK(cudaMemcpyAsync(counters, h_counters, sizeof h_counters, cudaMemcpyHostToDevice, 0));
+    CollapseArgs a;
+    a.left = left; a.right = right; a.node_lo = node_lo; a.node_hi = node_hi; a.count = count; a.sorted_prim = sorted_prim;
+    a.prim_lo = prim_lo; a.prim_hi = prim_hi; a.tri_verts = tri_verts; a.nodes8 = out.bvh8; a.tri_verts8 = out.tri_verts8;
+    a.n_prims_total = n;
+    a.max_leaf = MAX_LEAF_CAP;        // LJ_MAX_LEAF: experiment knob (1..3)
+    if (const char *e = getenv("LJ_MAX_LEAF")) { int v = atoi(e); if (v >= 1 && v <= MAX_LEAF_CAP) a.max_leaf = v; }
+    a.open_leaves = 1;                // LJ_OPEN_LEAVES=0: experiment knob
+    if (const char *e = getenv("LJ_OPEN_LEAVES")) a.open_leaves = atoi(e) != 0;
+    bool coop = true;
+    if (const char *e = getenv("LJ_BVH8_COOP")) coop = atoi(e) != 0;
+    if (coop) {
+        int per_sm = 0, dev = 0, sm_count = 0;
+        CK(cudaGetDevice(&dev));
+        CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_collapse_all, 64, 0));
+        int grid = per_sm * sm_count;
+        if (grid < 1) { snprintf(err, 256, "bvh8 collapse: no resident block for the cooperative launch"); return -1; }
+        const int want = (n / 4 + 63) / 64 + 1;         // the widest level holds fewer than n / 4 nodes
+        if (grid > want) grid = want;
+        void *args[] = {&q0, &q1, &counters, &d_root2, &a};
+        CK(cudaLaunchCooperativeKernel((const void *)k_collapse_all, dim3(grid), dim3(64), args, 0, 0));
+    } else {
+        k_collapse_root<<<1, 1>>>(q0, d_root2, n);
+        int n_items = 1, levels = 0;
+        while (n_items > 0) {
+            int *n_out = counters + 2 + (levels + 1) % 3;
+            CK(cudaMemsetAsync(n_out, 0, sizeof(int), 0));
+            k_collapse_level<<<(n_items + 63) / 64, 64>>>(q0, n_items, q1, n_out, counters, a);
+            CK(cudaGetLastError());
+            CK(cudaMemcpy(&n_items, n_out, sizeof(int), cudaMemcpyDeviceToHost));
+            Work *t = q0; q0 = q1; q1 = t;
+            if (++levels > 128) break;
+        }
+        CK(cudaMemcpyAsync(counters + 5, &levels, sizeof(int), cudaMemcpyHostToDevice, 0));
+        CK(cudaStreamSynchronize(0));       // `levels` is a stack variable
     }
-    out.num_bvh8 = h_counters[0];
-    out.num_slots8 = h_counters[1];
-    out.levels8 = levels;
-    lj_free(counters); lj_free(q0); lj_free(q1);
-    if (out.num_slots8 != n) { snprintf(err, 256, "bvh8 collapse lost primitives: %d of %d", out.num_slots8, n); return -1; }
+    lj_free(q0); lj_free(q1);
     return 0;
 }

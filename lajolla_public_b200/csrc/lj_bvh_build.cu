@@ -11,7 +11,9 @@
 
 #include <cub/device/device_radix_sort.cuh>
 #include <cub/device/device_scan.cuh>
+#include <cooperative_groups.h>
 #include <cstdlib>
+#include <cstring>
 #include <cfloat>
 #include <cstdio>
 #include <vector>
@@ -392,6 +394,143 @@ __global__ void k_ploc_compact(const int *m_ptr, int m_upper, int *m_next, const
     cid2[p] = cid[i]; ccount2[p] = ccount[i]; clo2[p] = clo[i]; chi2[p] = chi[i];
 }
 
+// The rounds above as ONE cooperative launch (the default): the same search, merge rule and order-preserving compaction,
+// with three grid barriers per round in place of five launches and a host read-back every few rounds.  A round is
+//   A  nearest neighbour of every cluster (chunks of PLOC_B clusters, the chunk + 2 * radius boxes staged in shared memory)
+//   B  merge decision per cluster, exclusive scan of (kept, created) inside the chunk, chunk totals to `chunk_sums`
+//   C  every chunk adds the totals of the chunks before it, creates its nodes and writes the kept clusters to the other buffer
+// Node ids come from the scan, so the tree is the same from run to run (the launch sequence takes them from an atomic).
+// Stops once at most `stop_at` clusters are left (k_ploc_tail finishes from there) and leaves them in buffer 0.
+// counter: [0] next node id, [1] clusters left, [2] rounds done, [3] 1 = a round made no progress.
+struct PlocBufs { int *cid[2], *cc[2]; float4 *clo[2], *chi[2]; };
+__global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int *lpos, unsigned long long *chunk_sums, int *counter,
+                                                        int *left, int *right, int *count, float4 *node_lo, float4 *node_hi,
+                                                        const int radius, const int stop_at) {
+    namespace cg = cooperative_groups;
+    cg::grid_group grid = cg::this_grid();
+    __shared__ float4 slo[PLOC_B + 2 * PLOC_RMAX], shi[PLOC_B + 2 * PLOC_RMAX];
+    __shared__ int warp_sums[PLOC_B / 32];
+    __shared__ unsigned long long s_pre[2];
+    const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
+    int m = counter[1], next_id = counter[0], cur = 0, rounds = 0;
+    bool stuck = false;
+    while (m > stop_at) {
+        const int chunks = (m + PLOC_B - 1) / PLOC_B;
+        const float4 *clo = b.clo[cur], *chi = b.chi[cur];
+        // ---- A: nearest neighbours ----
+        for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+            const int base = c * PLOC_B - radius;
+            __syncthreads();                        // the previous chunk's searches are over
+            for (int t = tid; t < PLOC_B + 2 * radius; t += PLOC_B) {
+                const int g = base + t;
+                if (g >= 0 && g < m) { slo[t] = clo[g]; shi[t] = chi[g]; }
+            }
+            __syncthreads();
+            const int i = c * PLOC_B + tid;
+            if (i < m) {
+                const int li = tid + radius;
+                const float4 lo = slo[li], hi = shi[li];
+                float best = FLT_MAX; int bj = -1;
+                const int o0 = i - radius < 0 ? -i : -radius, o1 = i + radius >= m ? m - 1 - i : radius;
+                for (int o = o0; o <= o1; o++) {
+                    if (o == 0) continue;
+                    const float a = union_area(lo, hi, slo[li + o], shi[li + o]);
+                    if (a < best) { best = a; bj = i + o; }     // ties keep the smaller j
+                }
+                nn[i] = bj;
+            }
+        }
+        grid.sync();
+        // ---- B: merge decisions, scan inside the chunk ----
+        for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+            const int i = c * PLOC_B + tid;
+            int keep = 0, creates = 0;
+            if (i < m) {
+                const int j = nn[i];
+                keep = 1;
+                if (j >= 0 && nn[j] == i) { if (i < j) creates = 1; else keep = 0; }
+            }
+            int x = keep | (creates << 16);         // both counts stay below 2^16 inside a chunk
+            const int v = x;
+#pragma unroll
+            for (int o = 1; o < 32; o <<= 1) { const int y = __shfl_up_sync(0xffffffffu, x, o); if (lane >= o) x += y; }
+            __syncthreads();                        // warp_sums of the previous chunk has been read
+            if (lane == 31) warp_sums[w] = x;
+            __syncthreads();
+            int before = 0, total = 0;
+#pragma unroll
+            for (int k = 0; k < PLOC_B / 32; k++) { const int ws = warp_sums[k]; if (k < w) before += ws; total += ws; }
+            if (i < m) lpos[i] = keep ? (int)((unsigned)(before + x - v) | (creates ? 0x80000000u : 0u)) : -1;      // creates lives in bit 31, created-before in bits 16..30
+            if (tid == 0) chunk_sums[c] = (unsigned long long)(total & 0xffff) | ((unsigned long long)(total >> 16) << 32);
+        }
+        grid.sync();
+        // ---- C: global positions, node creation, compaction into the other buffer ----
+        const int *cid = b.cid[cur], *cc = b.cc[cur];
+        int *cid2 = b.cid[cur ^ 1], *cc2 = b.cc[cur ^ 1];
+        float4 *clo2 = b.clo[cur ^ 1], *chi2 = b.chi[cur ^ 1];
+        unsigned long long tot = 0;
+        for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
+            __syncthreads();                        // s_pre of the previous chunk has been read
+            if (w == 0) {
+                unsigned long long pre = 0, all = 0;
+                for (int k = lane; k < chunks; k += 32) { const unsigned long long cs = chunk_sums[k]; all += cs; if (k < c) pre += cs; }
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) { pre += __shfl_xor_sync(0xffffffffu, pre, o); all += __shfl_xor_sync(0xffffffffu, all, o); }
+                if (lane == 0) { s_pre[0] = pre; s_pre[1] = all; }
+            }
+            __syncthreads();
+            const unsigned long long pre = s_pre[0];
+            tot = s_pre[1];
+            const int i = c * PLOC_B + tid;
+            if (i < m) {
+                const int lp = lpos[i];
+                if (lp != -1) {
+                    const int p = (int)(pre & 0xffffffffu) + (lp & 0xffff);
+                    int id = cid[i], cnt = cc[i];
+                    float4 lo = clo[i], hi = chi[i];
+                    if (lp < 0) {                   // bit 31: this cluster absorbs its partner
+                        const int j = nn[i];
+                        const float4 lo2 = clo[j], hi2 = chi[j];
+                        const int nid = next_id + (int)(pre >> 32) + ((lp >> 16) & 0x7fff);
+                        lo = make_float4(fminf(lo.x, lo2.x), fminf(lo.y, lo2.y), fminf(lo.z, lo2.z), 0.f);
+                        hi = make_float4(fmaxf(hi.x, hi2.x), fmaxf(hi.y, hi2.y), fmaxf(hi.z, hi2.z), 0.f);
+                        left[nid] = id; right[nid] = cid[j];
+                        cnt += cc[j];
+                        count[nid] = cnt; node_lo[nid] = lo; node_hi[nid] = hi;
+                        id = nid;
+                    }
+                    cid2[p] = id; cc2[p] = cnt; clo2[p] = lo; chi2[p] = hi;
+                }
+            }
+        }
+        if (blockIdx.x >= chunks) {                 // a block without a chunk this round still needs the totals
+            if (w == 0) {
+                unsigned long long all = 0;
+                for (int k = lane; k < chunks; k += 32) all += chunk_sums[k];
+#pragma unroll
+                for (int o = 16; o > 0; o >>= 1) all += __shfl_xor_sync(0xffffffffu, all, o);
+                if (lane == 0) s_pre[1] = all;
+            }
+            __syncthreads();
+            tot = s_pre[1];
+            __syncthreads();
+        }
+        const int m_new = (int)(tot & 0xffffffffu);
+        next_id += (int)(tot >> 32);
+        rounds++;
+        cur ^= 1;
+        if (m_new >= m || m_new < 1 || rounds > 4096) { stuck = true; break; }     // uniform over the grid
+        m = m_new;
+        grid.sync();
+    }
+    if (!stuck && cur == 1) {                       // hand the remaining (<= stop_at) clusters over in buffer 0
+        // every block has passed the last barrier of the loop, so buffer 1 is complete; only block 0 copies
+        if (blockIdx.x == 0)
+            for (int t = tid; t < m; t += PLOC_B) { b.cid[0][t] = b.cid[1][t]; b.cc[0][t] = b.cc[1][t]; b.clo[0][t] = b.clo[1][t]; b.chi[0][t] = b.chi[1][t]; }
+    }
+    if (blockIdx.x == 0 && tid == 0) { counter[0] = next_id; counter[1] = m; counter[2] = rounds; counter[3] = stuck ? 1 : 0; }
+}
+
 // All remaining PLOC rounds in ONE block once at most PLOC_TAIL clusters are left: the same search, merge rule
 // (mutually nearest pairs, ties keep the smaller index) and order-preserving compaction as the kernels above, with the
 // clusters in shared memory and block-wide scans instead of a launch sequence + a blocking read-back per round.  The
@@ -427,19 +566,32 @@ __global__ void __launch_bounds__(PLOC_TAIL) k_ploc_tail(const int *m_ptr, int *
     int next_id = *node_counter;
     __syncthreads();
     while (m > 1) {
-        int bj = -1;
-        if (t < m) {
-            const float4 lo = slo[t], hi = shi[t];
-            float best = FLT_MAX;
-            const int j0 = t - radius < 0 ? 0 : t - radius, j1 = t + radius >= m ? m - 1 : t + radius;
-            for (int j = j0; j <= j1; j++) {
-                if (j == t) continue;
-                const float a = union_area(lo, hi, slo[j], shi[j]);
-                if (a < best) { best = a; bj = j; }
+        // search: T = 2^k threads per cluster once the block has spare threads (T <= 32 divides the warp size, so a
+        // cluster's threads share a warp); each takes every T-th candidate, the (area, index) minimum is the sequential
+        // scan's result: smallest area, ties to the smaller index
+        int T = 1;
+        while (T < 32 && 2 * T * m <= PLOC_TAIL) T <<= 1;
+        {
+            const int c = t / T, sub = t & (T - 1);
+            float best = FLT_MAX; int sj = -1;
+            if (c < m) {
+                const float4 lo = slo[c], hi = shi[c];
+                const int j0 = c - radius < 0 ? 0 : c - radius, j1 = c + radius >= m ? m - 1 : c + radius;
+                for (int j = j0 + sub; j <= j1; j += T) {
+                    if (j == c) continue;
+                    const float a = union_area(lo, hi, slo[j], shi[j]);
+                    if (a < best) { best = a; sj = j; }
+                }
             }
-            snn[t] = bj;
+            for (int o = T >> 1; o > 0; o >>= 1) {
+                const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+                const int oj = __shfl_xor_sync(0xffffffffu, sj, o);
+                if (oj >= 0 && (sj < 0 || ob < best || (ob == best && oj < sj))) { best = ob; sj = oj; }
+            }
+            if (c < m && sub == 0) snn[c] = sj;
         }
         __syncthreads();
+        const int bj = t < m ? snn[t] : -1;
         int keep = t < m ? 1 : 0, creates = 0;
         float4 lo, hi; int id_l = 0, id_r = 0, c = 0;
         if (t < m) {
@@ -485,58 +637,91 @@ __global__ void k_lbvh_counts(int n, const int *left, const int *right, int *cou
 
 } // namespace
 
+// d_info (device): [0] receives the root id, [1] is set to 1 when a round made no progress (read back by the caller
+// together with the collapse counters: the build blocks on the device once, at its end).
 static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float4 *prim_hi,
-                      int *left, int *right, int *count, float4 *node_lo, float4 *node_hi, int *root_out, char *err) {
+                      int *left, int *right, int *count, float4 *node_lo, float4 *node_hi, int *d_info, char *err) {
     int *cid[2] = {nullptr, nullptr}, *cc[2] = {nullptr, nullptr}, *nn = nullptr, *valid = nullptr, *pos = nullptr, *counter = nullptr;
     float4 *clo[2] = {nullptr, nullptr}, *chi[2] = {nullptr, nullptr};
+    unsigned long long *chunk_sums = nullptr;
     void *tmp = nullptr; size_t tmp_bytes = 0;
     for (int b = 0; b < 2; b++) {
         CK(lj_malloc(&cid[b], 4 * (size_t)n)); CK(lj_malloc(&cc[b], 4 * (size_t)n));
         CK(lj_malloc(&clo[b], sizeof(float4) * n)); CK(lj_malloc(&chi[b], sizeof(float4) * n));
     }
     CK(lj_malloc(&nn, 4 * (size_t)n)); CK(lj_malloc(&valid, 4 * (size_t)(n + 1))); CK(lj_malloc(&pos, 4 * (size_t)(n + 1)));
-    CK(lj_malloc(&counter, 3 * 4));             // [0] next node id, [1], [2] cluster count before / after a round (alternating)
+    CK(lj_malloc(&counter, 4 * 4));             // launch sequence: [0] next node id, [1], [2] cluster count before / after a round (alternating); cooperative: see k_ploc_rounds
     {
-        const int init[3] = {0, n, n};
-        CK(cudaMemcpy(counter, init, sizeof init, cudaMemcpyHostToDevice));
+        const int init[4] = {0, n, n, 0};
+        CK(cudaMemcpyAsync(counter, init, sizeof init, cudaMemcpyHostToDevice, 0));      // (pageable source: staged before the call returns)
     }
-    CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, valid, pos, n + 1));
-    CK(lj_malloc(&tmp, tmp_bytes));
     k_ploc_init<<<(n + 255) / 256, 256>>>(n, vals, prim_lo, prim_hi, cid[0], cc[0], clo[0], chi[0]);
-    int m = n, cur = 0, rounds = 0;     // m: the last count the host has seen
     int radius = PLOC_R;
     if (const char *e = getenv("LJ_PLOC_R")) { int v = atoi(e); if (v >= 1 && v <= PLOC_RMAX) radius = v; }
     const bool use_tail = !getenv("LJ_PLOC_NO_TAIL");
     const bool trace = getenv("LJ_BVH_TRACE") != nullptr;
-    int batch = 4;                      // rounds between two read-backs of the cluster count
-    if (const char *e = getenv("LJ_PLOC_BATCH")) { int v = atoi(e); if (v >= 1 && v <= 64) batch = v; }
-    while (m > 1) {
-        int *m_in = counter + 1 + (rounds & 1);
-        if (use_tail && m <= PLOC_TAIL) {
-            k_ploc_tail<<<1, PLOC_TAIL>>>(m_in, cid[cur], cc[cur], clo[cur], chi[cur], left, right, count, node_lo, node_hi, counter, radius);
-            CK(cudaGetLastError());
-            break;
+    bool coop = use_tail;                       // LJ_PLOC_COOP=0: the launch sequence with a read-back every LJ_PLOC_BATCH rounds
+    if (const char *e = getenv("LJ_PLOC_COOP")) coop = coop && atoi(e) != 0;
+    int cur = 0;
+    if (coop) {
+        const int chunks = (n + PLOC_B - 1) / PLOC_B;
+        if (n > PLOC_TAIL) {
+            int per_sm = 0, dev = 0, sm_count = 0;
+            CK(cudaGetDevice(&dev));
+            CK(cudaDeviceGetAttribute(&sm_count, cudaDevAttrMultiProcessorCount, dev));
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ploc_rounds, PLOC_B, 0));
+            int grid = per_sm * sm_count;
+            if (grid < 1) { snprintf(err, 256, "PLOC: no resident block for the cooperative rounds"); return -1; }
+            if (grid > chunks) grid = chunks;
+            CK(lj_malloc(&chunk_sums, 8 * (size_t)chunks));
+            PlocBufs bufs;
+            for (int b = 0; b < 2; b++) { bufs.cid[b] = cid[b]; bufs.cc[b] = cc[b]; bufs.clo[b] = clo[b]; bufs.chi[b] = chi[b]; }
+            int *lpos = valid; int stop_at = PLOC_TAIL; int rad = radius;
+            void *args[] = {&bufs, &nn, &lpos, &chunk_sums, &counter, &left, &right, &count, &node_lo, &node_hi, &rad, &stop_at};
+            CK(cudaLaunchCooperativeKernel((const void *)k_ploc_rounds, dim3(grid), dim3(PLOC_B), args, 0, 0));
         }
-        const int m_upper = m;
-        for (int b = 0; b < batch; b++) {
-            m_in = counter + 1 + (rounds & 1);
-            int *m_out = counter + 1 + ((rounds + 1) & 1);
-            k_ploc_nn<<<(m_upper + PLOC_B - 1) / PLOC_B, PLOC_B>>>(m_in, clo[cur], chi[cur], nn, radius);
-            k_ploc_merge<<<(m_upper + 1 + 255) / 256, 256>>>(m_in, m_upper, nn, cid[cur], cc[cur], clo[cur], chi[cur], valid, left, right, count, node_lo, node_hi, counter);
-            CK(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, valid, pos, m_upper + 1));
-            k_ploc_compact<<<(m_upper + 255) / 256, 256>>>(m_in, m_upper, m_out, valid, pos, cid[cur], cc[cur], clo[cur], chi[cur], cid[1 - cur], cc[1 - cur], clo[1 - cur], chi[1 - cur]);
-            cur = 1 - cur;
-            if (++rounds > 4096) { snprintf(err, 256, "PLOC did not converge"); return -1; }
+        k_ploc_tail<<<1, PLOC_TAIL>>>(counter + 1, cid[0], cc[0], clo[0], chi[0], left, right, count, node_lo, node_hi, counter, radius);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(d_info + 1, counter + 3, 4, cudaMemcpyDeviceToDevice, 0));
+        if (trace) {
+            int h[4];
+            CK(cudaMemcpy(h, counter, sizeof h, cudaMemcpyDeviceToHost));
+            fprintf(stderr, "[bvh]   PLOC: %d cooperative rounds down to %d clusters, then the one-block tail\n", h[2], n > PLOC_TAIL ? PLOC_TAIL : n);
         }
-        int m_new = 0;
-        CK(cudaMemcpy(&m_new, counter + 1 + (rounds & 1), 4, cudaMemcpyDeviceToHost));
-        if (m_new >= m || m_new < 1) { snprintf(err, 256, "PLOC made no progress (%d -> %d clusters)", m, m_new); return -1; }
-        if (trace) fprintf(stderr, "[bvh]   PLOC after round %d: %d -> %d clusters\n", rounds, m, m_new);
-        m = m_new;
+    } else {
+        CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, valid, pos, n + 1));
+        CK(lj_malloc(&tmp, tmp_bytes));
+        int m = n, rounds = 0;              // m: the last count the host has seen
+        int batch = 4;                      // rounds between two read-backs of the cluster count
+        if (const char *e = getenv("LJ_PLOC_BATCH")) { int v = atoi(e); if (v >= 1 && v <= 64) batch = v; }
+        while (m > 1) {
+            int *m_in = counter + 1 + (rounds & 1);
+            if (use_tail && m <= PLOC_TAIL) {
+                k_ploc_tail<<<1, PLOC_TAIL>>>(m_in, cid[cur], cc[cur], clo[cur], chi[cur], left, right, count, node_lo, node_hi, counter, radius);
+                CK(cudaGetLastError());
+                break;
+            }
+            const int m_upper = m;
+            for (int b = 0; b < batch; b++) {
+                m_in = counter + 1 + (rounds & 1);
+                int *m_out = counter + 1 + ((rounds + 1) & 1);
+                k_ploc_nn<<<(m_upper + PLOC_B - 1) / PLOC_B, PLOC_B>>>(m_in, clo[cur], chi[cur], nn, radius);
+                k_ploc_merge<<<(m_upper + 1 + 255) / 256, 256>>>(m_in, m_upper, nn, cid[cur], cc[cur], clo[cur], chi[cur], valid, left, right, count, node_lo, node_hi, counter);
+                CK(cub::DeviceScan::ExclusiveSum(tmp, tmp_bytes, valid, pos, m_upper + 1));
+                k_ploc_compact<<<(m_upper + 255) / 256, 256>>>(m_in, m_upper, m_out, valid, pos, cid[cur], cc[cur], clo[cur], chi[cur], cid[1 - cur], cc[1 - cur], clo[1 - cur], chi[1 - cur]);
+                cur = 1 - cur;
+                if (++rounds > 4096) { snprintf(err, 256, "PLOC did not converge"); return -1; }
+            }
+            int m_new = 0;
+            CK(cudaMemcpy(&m_new, counter + 1 + (rounds & 1), 4, cudaMemcpyDeviceToHost));
+            if (m_new >= m || m_new < 1) { snprintf(err, 256, "PLOC made no progress (%d -> %d clusters)", m, m_new); return -1; }
+            if (trace) fprintf(stderr, "[bvh]   PLOC after round %d: %d -> %d clusters\n", rounds, m, m_new);
+            m = m_new;
+        }
     }
-    CK(cudaMemcpy(root_out, cid[cur], 4, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpyAsync(d_info, cid[cur], 4, cudaMemcpyDeviceToDevice, 0));
     for (int b = 0; b < 2; b++) { lj_free(cid[b]); lj_free(cc[b]); lj_free(clo[b]); lj_free(chi[b]); }
-    lj_free(nn); lj_free(valid); lj_free(pos); lj_free(counter); lj_free(tmp);
+    lj_free(nn); lj_free(valid); lj_free(pos); lj_free(counter); lj_free(tmp); lj_free(chunk_sums);
     return 0;
 }
 
@@ -554,13 +739,13 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
     float4 *prim_lo = nullptr, *prim_hi = nullptr;
     float *bounds = nullptr;
     CK(lj_malloc(&prim_lo, sizeof(float4) * n)); CK(lj_malloc(&prim_hi, sizeof(float4) * n));
-    CK(lj_malloc(&bounds, sizeof(float) * 6));
-    float init_b[6] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX};
-    CK(cudaMemcpy(bounds, init_b, sizeof init_b, cudaMemcpyHostToDevice));
+    // bounds[0..5]: scene AABB; bounds[8..15] reinterpreted as ints: the results the host reads back ONCE at the end of the
+    // build (root id, PLOC status, collapse counters), see lj_bvh_build_refs
+    CK(lj_malloc(&bounds, sizeof(float) * 16));
+    float init_b[16] = {FLT_MAX, FLT_MAX, FLT_MAX, -FLT_MAX, -FLT_MAX, -FLT_MAX, 0, 0, 0, 0, 0, 0, 0, 0, 0, 0};
+    CK(cudaMemcpyAsync(bounds, init_b, sizeof init_b, cudaMemcpyHostToDevice, 0));
     k_prim_bounds<<<G, B>>>(in.num_tris, in.num_spheres, in.positions, in.indices, in.tri_shape, in.shapes, in.spheres, prim_lo, prim_hi, bounds);
     CK(cudaGetLastError());
-    CK(cudaMemcpy(out.lo, bounds, sizeof(float) * 3, cudaMemcpyDeviceToHost));
-    CK(cudaMemcpy(out.hi, bounds + 3, sizeof(float) * 3, cudaMemcpyDeviceToHost));
     pt.mark("primitive bounds");
 
     // ---- triangle pre-splitting: primitives -> references (see k_split_refs) ----
@@ -571,6 +756,11 @@ int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err) {
         // 9.8 -> 7.0 primitive tests per ray for 15.0 -> 18.0 node visits and is 9 % slower (profiles/r01_experiments.md)
         const char *e = getenv("LJ_SPLIT_ALPHA");
         double alpha = e ? atof(e) : 0.0;
+        if (alpha > 0) {                            // the split threshold needs the scene box on the host now
+            float hb[6];
+            CK(cudaMemcpy(hb, bounds, sizeof hb, cudaMemcpyDeviceToHost));
+            for (int a = 0; a < 3; a++) { out.lo[a] = hb[a]; out.hi[a] = hb[3 + a]; }
+        }
         const double sx = out.hi[0] - out.lo[0], sy = out.hi[1] - out.lo[1], sz = out.hi[2] - out.lo[2];
         const double scene_area = sx * sy + sy * sz + sz * sx;
         if (alpha > 0 && in.num_tris > 0 && scene_area > 0) {
@@ -614,6 +804,7 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     const int G = (n + B - 1) / B;
     out.num_prims = n;
     BvhPhaseTimer pt;
+    int *d_info = (int *)(bounds + 8);      // [0] root id, [1] PLOC status, [2..7] collapse counters
     float4 *node_lo = nullptr, *node_hi = nullptr;
     unsigned long long *keys = nullptr, *keys2 = nullptr;
     int *vals = nullptr, *vals2 = nullptr, *left = nullptr, *right = nullptr, *par_i = nullptr, *par_l = nullptr, *flags = nullptr, *count = nullptr;
@@ -651,9 +842,9 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
             k_fit<<<G, B>>>(n, vals2, prim_lo, prim_hi, left, right, par_i, par_l, flags, node_lo, node_hi);
             CK(cudaGetLastError());
             k_lbvh_counts<<<G, B>>>(n, left, right, count);
-            out.bvh2_root = 0;
+            CK(cudaMemsetAsync(d_info, 0, 2 * sizeof(int), 0));         // root id 0
         } else {
-            if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, &out.bvh2_root, err) != 0) { free_temps(); return -1; }
+            if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, d_info, err) != 0) { free_temps(); return -1; }
         }
         pt.mark("PLOC");
         CK(lj_malloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
@@ -661,13 +852,29 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
         CK(cudaGetLastError());
         out.num_bvh2 = n - 1;
     }
-    CK(cudaStreamSynchronize(0));
     pt.mark("emit binary tree");
     // the 8-wide collapse consumes the binary tree (lj_bvh8_build.cu)
-    int rc = lj_bvh8_collapse(n, out.bvh2_root, out.tri_verts, left, right, count, node_lo, node_hi, vals2, prim_lo, prim_hi, out, err);
+    int rc = lj_bvh8_collapse(n, d_info, out.tri_verts, left, right, count, node_lo, node_hi, vals2, prim_lo, prim_hi, out, d_info + 2, err);
     pt.mark("8-wide collapse");
+    // the one blocking read-back of the build: scene box, root id, PLOC status, collapse counters
+    float h_res[16];
+    if (rc == 0) {
+        cudaError_t e_ = cudaMemcpy(h_res, bounds, sizeof h_res, cudaMemcpyDeviceToHost);
+        if (e_ != cudaSuccess) { snprintf(err, 256, "BVH build: %s", cudaGetErrorString(e_)); rc = -1; }
+    }
     free_temps();
-    return rc;
+    if (rc != 0) return rc;
+    int h_info[8];
+    memcpy(h_info, h_res + 8, sizeof h_info);
+    for (int a = 0; a < 3; a++) { out.lo[a] = h_res[a]; out.hi[a] = h_res[3 + a]; }
+    out.bvh2_root = h_info[0];
+    if (h_info[1] != 0) { snprintf(err, 256, "PLOC made no progress (a round merged nothing)"); return -1; }
+    out.num_bvh8 = h_info[2];
+    out.num_slots8 = h_info[3];
+    out.levels8 = h_info[7];
+    if (out.levels8 > 128) { snprintf(err, 256, "bvh8 collapse did not terminate"); return -1; }
+    if (out.num_slots8 != n) { snprintf(err, 256, "bvh8 collapse lost primitives: %d of %d", out.num_slots8, n); return -1; }
+    return 0;
 }
 
 void lj_bvh_free(BvhBuildOutput &out) {

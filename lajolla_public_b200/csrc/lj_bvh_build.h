@@ -25,7 +25,8 @@ struct BvhBuildOutput {
 int lj_bvh_build(const BvhBuildInput &in, BvhBuildOutput &out, char *err /* >= 256 bytes */);
 void lj_bvh_free(BvhBuildOutput &out);
 
-// 8-wide collapse + quantisation of the binary tree (device arrays of the builder)
-int lj_bvh8_collapse(int n, int root2, const float4 *tri_verts, const int *left, const int *right, const int *count,
+// 8-wide collapse + quantisation of the binary tree (device arrays of the builder); d_root2 and d_counters are device
+// pointers (root id in, 6 counters out: the caller reads them back), see lj_bvh8_build.cu
+int lj_bvh8_collapse(int n, const int *d_root2, const float4 *tri_verts, const int *left, const int *right, const int *count,
                      const float4 *node_lo, const float4 *node_hi, const int *sorted_prim,
-                     const float4 *prim_lo, const float4 *prim_hi, BvhBuildOutput &out, char *err);
+                     const float4 *prim_lo, const float4 *prim_hi, BvhBuildOutput &out, int *d_counters, char *err);

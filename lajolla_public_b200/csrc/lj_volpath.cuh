@@ -33,36 +33,60 @@ LJ_D d3 volume_blend(double scale, double dx, double dy, double dz, d3 v000, d3 
                     v111 * (dx * dy * dz));
 }
 
+// the blend above for a one-channel f32 grid
+LJ_D double volume_blend_grey(const float *gf, double scale, double dx, double dy, double dz, size_t i000, size_t i001, size_t i010, size_t i011,
+                              size_t i100, size_t i101, size_t i110, size_t i111) {
+    const double a000 = (double)__ldg(gf + i000), a001 = (double)__ldg(gf + i001), a010 = (double)__ldg(gf + i010), a011 = (double)__ldg(gf + i011);
+    const double a100 = (double)__ldg(gf + i100), a101 = (double)__ldg(gf + i101), a110 = (double)__ldg(gf + i110), a111 = (double)__ldg(gf + i111);
+    return scale * (a000 * ((1 - dx) * (1 - dy) * (1 - dz)) +
+                    a001 * (dx * (1 - dy) * (1 - dz)) +
+                    a010 * ((1 - dx) * dy * (1 - dz)) +
+                    a011 * (dx * dy * (1 - dz)) +
+                    a100 * ((1 - dx) * (1 - dy) * dz) +
+                    a101 * (dx * (1 - dy) * dz) +
+                    a110 * ((1 - dx) * dy * dz) +
+                    a111 * (dx * dy * dz));
+}
+
 // ---- volume.h:45-81: trilinear lookup in double, zero outside the grid's box ----
-LJ_D d3 volume_lookup(const DScene &sc, const lj_volume &v, d3 p) {
-    if (v.kind == LJ_VOLUME_CONSTANT) return mk3(v.value[0], v.value[1], v.value[2]);
+// the cell of a point: corner indices and fractional offsets (volume.h:46-66); false outside the box
+struct GridCell { size_t i000, i001, i010, i011, i100, i101, i110, i111; double dx, dy, dz; };
+LJ_D bool grid_cell(const lj_volume &v, d3 p, GridCell &c) {
     d3 pmin = mk3(v.p_min[0], v.p_min[1], v.p_min[2]), pmax = mk3(v.p_max[0], v.p_max[1], v.p_max[2]);
     d3 pn = (p - pmin) / (pmax - pmin);
-    if (pn.x < 0 || pn.x > 1 || pn.y < 0 || pn.y > 1 || pn.z < 0 || pn.z > 1) return mk3(0.0);
+    if (pn.x < 0 || pn.x > 1 || pn.y < 0 || pn.y > 1 || pn.z < 0 || pn.z > 1) return false;
     const int rx = v.resolution[0], ry = v.resolution[1], rz = v.resolution[2];
     pn.x *= (double)(rx - 1); pn.y *= (double)(ry - 1); pn.z *= (double)(rz - 1);
     int x0 = clampi((int)pn.x, 0, rx - 1), y0 = clampi((int)pn.y, 0, ry - 1), z0 = clampi((int)pn.z, 0, rz - 1);
     int x1 = clampi(x0 + 1, 0, rx - 1), y1 = clampi(y0 + 1, 0, ry - 1), z1 = clampi(z0 + 1, 0, rz - 1);
-    double dx = pn.x - x0, dy = pn.y - y0, dz = pn.z - z0;
-    const size_t i000 = (size_t)(z0 * ry + y0) * rx + x0, i001 = (size_t)(z0 * ry + y0) * rx + x1;
-    const size_t i010 = (size_t)(z0 * ry + y1) * rx + x0, i011 = (size_t)(z0 * ry + y1) * rx + x1;
-    const size_t i100 = (size_t)(z1 * ry + y0) * rx + x0, i101 = (size_t)(z1 * ry + y0) * rx + x1;
-    const size_t i110 = (size_t)(z1 * ry + y1) * rx + x0, i111 = (size_t)(z1 * ry + y1) * rx + x1;
+    c.dx = pn.x - x0; c.dy = pn.y - y0; c.dz = pn.z - z0;
+    c.i000 = (size_t)(z0 * ry + y0) * rx + x0; c.i001 = (size_t)(z0 * ry + y0) * rx + x1;
+    c.i010 = (size_t)(z0 * ry + y1) * rx + x0; c.i011 = (size_t)(z0 * ry + y1) * rx + x1;
+    c.i100 = (size_t)(z1 * ry + y0) * rx + x0; c.i101 = (size_t)(z1 * ry + y0) * rx + x1;
+    c.i110 = (size_t)(z1 * ry + y1) * rx + x0; c.i111 = (size_t)(z1 * ry + y1) * rx + x1;
+    return true;
+}
+// A volume whose three channels are equal everywhere (a constant with equal components, or a grid stored as one f32
+// channel): one channel of volume_lookup's result, which is all of them.
+LJ_D bool volume_is_grey(const lj_volume &v) {
+    return v.kind == LJ_VOLUME_CONSTANT ? (v.value[0] == v.value[1] && v.value[0] == v.value[2]) : v._pad == 1;
+}
+LJ_D double volume_lookup_grey(const DScene &sc, const lj_volume &v, d3 p) {
+    if (v.kind == LJ_VOLUME_CONSTANT) return v.value[0];
+    GridCell c;
+    if (!grid_cell(v, p, c)) return 0.0;
+    return volume_blend_grey(sc.grid_f32 + v.data_offset, v.scale, c.dx, c.dy, c.dz, c.i000, c.i001, c.i010, c.i011, c.i100, c.i101, c.i110, c.i111);
+}
+LJ_D d3 volume_lookup(const DScene &sc, const lj_volume &v, d3 p) {
+    if (v.kind == LJ_VOLUME_CONSTANT) return mk3(v.value[0], v.value[1], v.value[2]);
+    GridCell c;
+    if (!grid_cell(v, p, c)) return mk3(0.0);
+    const double dx = c.dx, dy = c.dy, dz = c.dz;
+    const size_t i000 = c.i000, i001 = c.i001, i010 = c.i010, i011 = c.i011, i100 = c.i100, i101 = c.i101, i110 = c.i110, i111 = c.i111;
     if (v._pad == 1) {
         // one f32 channel (the three channels of the Spectrum grid are equal): the same expression once; every
         // channel of the reference's result is this value
-        const float *gf = sc.grid_f32 + v.data_offset;
-        const double a000 = (double)__ldg(gf + i000), a001 = (double)__ldg(gf + i001), a010 = (double)__ldg(gf + i010), a011 = (double)__ldg(gf + i011);
-        const double a100 = (double)__ldg(gf + i100), a101 = (double)__ldg(gf + i101), a110 = (double)__ldg(gf + i110), a111 = (double)__ldg(gf + i111);
-        const double r = v.scale * (a000 * ((1 - dx) * (1 - dy) * (1 - dz)) +
-                                    a001 * (dx * (1 - dy) * (1 - dz)) +
-                                    a010 * ((1 - dx) * dy * (1 - dz)) +
-                                    a011 * (dx * dy * (1 - dz)) +
-                                    a100 * ((1 - dx) * (1 - dy) * dz) +
-                                    a101 * (dx * (1 - dy) * dz) +
-                                    a110 * ((1 - dx) * dy * dz) +
-                                    a111 * (dx * dy * dz));
-        return mk3(r);
+        return mk3(volume_blend_grey(sc.grid_f32 + v.data_offset, v.scale, dx, dy, dz, i000, i001, i010, i011, i100, i101, i110, i111));
     }
     d3 v000, v001, v010, v011, v100, v101, v110, v111;
     if (v._pad == 3) {
