@@ -275,6 +275,19 @@ int lj_scene_create_single(lj_ctx *ctx, const lj_scene_desc *desc, uint32_t flag
             }
         }
     } else need_f64_grids = true;
+    {   // grey scene: equal channels in every medium (host mirror of medium_is_grey, after the grids got their storage marker)
+        auto vol_grey = [](const lj_volume &v) { return v.kind == LJ_VOLUME_CONSTANT ? (v.value[0] == v.value[1] && v.value[0] == v.value[2]) : v._pad == 1; };
+        s->media_grey = !dev_media.empty();
+        for (const lj_medium &m : dev_media) {
+            bool g;
+            if (m.kind == LJ_MEDIUM_HOMOGENEOUS)
+                g = m.sigma_a[0] == m.sigma_a[1] && m.sigma_a[0] == m.sigma_a[2] && m.sigma_s[0] == m.sigma_s[1] && m.sigma_s[0] == m.sigma_s[2];
+            else
+                g = vol_grey(m.density) && vol_grey(m.albedo) &&
+                    (m.density.kind == LJ_VOLUME_CONSTANT || (m.density.max_data[0] == m.density.max_data[1] && m.density.max_data[0] == m.density.max_data[2]));
+            s->media_grey = s->media_grey && g;
+        }
+    }
     Uploader up;
 #define UP(field, cnt) up.add(desc->field, (size_t)(cnt), &d.field);
     UP(shapes, desc->num_shapes) UP(lights, desc->num_lights) UP(materials, desc->num_materials)

@@ -418,27 +418,37 @@ __global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int
         const int chunks = (m + PLOC_B - 1) / PLOC_B;
         const float4 *clo = b.clo[cur], *chi = b.chi[cur];
         // ---- A: nearest neighbours ----
-        for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
-            const int base = c * PLOC_B - radius;
+        // T = 2^k threads per cluster once the grid has spare threads (as in k_ploc_tail): a block searches for PLOC_B / T
+        // clusters, each thread takes every T-th candidate, the (area, index) minimum is the sequential scan's result
+        int T = 1;
+        while (T < 32 && (long long)2 * T * m <= (long long)gridDim.x * PLOC_B) T <<= 1;
+        const int per_block = PLOC_B / T, chunks_a = (m + per_block - 1) / per_block;
+        for (int c = blockIdx.x; c < chunks_a; c += gridDim.x) {
+            const int first = c * per_block, base = first - radius;
             __syncthreads();                        // the previous chunk's searches are over
-            for (int t = tid; t < PLOC_B + 2 * radius; t += PLOC_B) {
+            for (int t = tid; t < per_block + 2 * radius; t += PLOC_B) {
                 const int g = base + t;
                 if (g >= 0 && g < m) { slo[t] = clo[g]; shi[t] = chi[g]; }
             }
             __syncthreads();
-            const int i = c * PLOC_B + tid;
+            const int i = first + tid / T, sub = tid & (T - 1);
+            float best = FLT_MAX; int bj = -1;
             if (i < m) {
-                const int li = tid + radius;
+                const int li = tid / T + radius;
                 const float4 lo = slo[li], hi = shi[li];
-                float best = FLT_MAX; int bj = -1;
                 const int o0 = i - radius < 0 ? -i : -radius, o1 = i + radius >= m ? m - 1 - i : radius;
-                for (int o = o0; o <= o1; o++) {
+                for (int o = o0 + sub; o <= o1; o += T) {
                     if (o == 0) continue;
                     const float a = union_area(lo, hi, slo[li + o], shi[li + o]);
                     if (a < best) { best = a; bj = i + o; }     // ties keep the smaller j
                 }
-                nn[i] = bj;
             }
+            for (int o = T >> 1; o > 0; o >>= 1) {
+                const float ob = __shfl_xor_sync(0xffffffffu, best, o);
+                const int oj = __shfl_xor_sync(0xffffffffu, bj, o);
+                if (oj >= 0 && (bj < 0 || ob < best || (ob == best && oj < bj))) { best = ob; bj = oj; }
+            }
+            if (i < m && sub == 0) nn[i] = bj;
         }
         grid.sync();
         // ---- B: merge decisions, scan inside the chunk ----
@@ -672,7 +682,11 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
             CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_ploc_rounds, PLOC_B, 0));
             int grid = per_sm * sm_count;
             if (grid < 1) { snprintf(err, 256, "PLOC: no resident block for the cooperative rounds"); return -1; }
-            if (grid > chunks) grid = chunks;
+            // blocks beyond one per chunk still help: the search of a round spreads over all threads of the grid
+            int want = sm_count * 4;
+            if (const char *e = getenv("LJ_PLOC_GRID")) { int v = atoi(e); if (v >= 1) want = v; }
+            if (want < 1) want = 1;
+            if (grid > want) grid = want;
             CK(lj_malloc(&chunk_sums, 8 * (size_t)chunks));
             PlocBufs bufs;
             for (int b = 0; b < 2; b++) { bufs.cid[b] = cid[b]; bufs.cc[b] = cc[b]; bufs.clo[b] = clo[b]; bufs.chi[b] = chi[b]; }
@@ -680,13 +694,20 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
             void *args[] = {&bufs, &nn, &lpos, &chunk_sums, &counter, &left, &right, &count, &node_lo, &node_hi, &rad, &stop_at};
             CK(cudaLaunchCooperativeKernel((const void *)k_ploc_rounds, dim3(grid), dim3(PLOC_B), args, 0, 0));
         }
+        std::chrono::steady_clock::time_point t_a, t_b;
+        int h[4] = {0, 0, 0, 0};
+        if (trace) {
+            CK(cudaStreamSynchronize(0)); t_a = std::chrono::steady_clock::now();
+            CK(cudaMemcpy(h, counter, sizeof h, cudaMemcpyDeviceToHost));
+            t_b = std::chrono::steady_clock::now();
+        }
         k_ploc_tail<<<1, PLOC_TAIL>>>(counter + 1, cid[0], cc[0], clo[0], chi[0], left, right, count, node_lo, node_hi, counter, radius);
         CK(cudaGetLastError());
         CK(cudaMemcpyAsync(d_info + 1, counter + 3, 4, cudaMemcpyDeviceToDevice, 0));
         if (trace) {
-            int h[4];
-            CK(cudaMemcpy(h, counter, sizeof h, cudaMemcpyDeviceToHost));
-            fprintf(stderr, "[bvh]   PLOC: %d cooperative rounds down to %d clusters, then the one-block tail\n", h[2], n > PLOC_TAIL ? PLOC_TAIL : n);
+            CK(cudaStreamSynchronize(0));
+            const double tail_ms = std::chrono::duration<double, std::milli>(std::chrono::steady_clock::now() - t_b).count();
+            fprintf(stderr, "[bvh]   PLOC: %d cooperative rounds down to %d clusters, then the one-block tail (%.3f ms)\n", n > PLOC_TAIL ? h[2] : 0, h[1], tail_ms);
         }
     } else {
         CK(cub::DeviceScan::ExclusiveSum(nullptr, tmp_bytes, valid, pos, n + 1));
@@ -818,11 +839,19 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     CK(lj_malloc(&vals, 4 * (size_t)n)); CK(lj_malloc(&vals2, 4 * (size_t)n));
     k_morton<<<G, B>>>(n, prim_lo, prim_hi, bounds, keys, vals);
     CK(cudaGetLastError());
+    // PLOC only needs the primitives in an order that keeps neighbours in space close in the array: up to 2^20 primitives
+    // the top 32 of the 63 code bits do that (4 radix passes instead of 8; equal prefixes stay in input order, the sort is
+    // stable).  The radix-tree builder reads the sorted codes themselves and gets all 63.  LJ_SORT_BITS overrides.
+    const char *bsel = getenv("LJ_BUILDER");       // "lbvh" keeps the plain radix tree; default PLOC
+    const bool lbvh = bsel && bsel[0] == 'l';
+    int sort_bits = (lbvh || n > (1 << 20)) ? 63 : 32;
+    if (const char *e = getenv("LJ_SORT_BITS")) { int v = atoi(e); if (v >= 8 && v <= 63 && !lbvh) sort_bits = v; }
     size_t tmp_bytes = 0;
-    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
+    CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 63 - sort_bits, 63));
     CK(lj_malloc(&tmp, tmp_bytes));
-    CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 0, 63));
-    pt.mark("morton + radix sort");
+    pt.mark("morton codes");
+    CK(cub::DeviceRadixSort::SortPairs(tmp, tmp_bytes, keys, keys2, vals, vals2, n, 63 - sort_bits, 63));
+    pt.mark("radix sort");
 
     CK(lj_malloc(&out.tri_verts, sizeof(float4) * 3 * (size_t)n));
     k_emit_prims<<<G, B>>>(n, in.num_tris, vals2, ref_prim, in.positions, in.indices, in.tri_shape, in.shapes, in.spheres, out.tri_verts);
@@ -835,8 +864,7 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
         CK(lj_malloc(&flags, 4 * (size_t)n)); CK(cudaMemset(flags, 0, 4 * (size_t)n));
         CK(lj_malloc(&node_lo, sizeof(float4) * n)); CK(lj_malloc(&node_hi, sizeof(float4) * n));
         CK(lj_malloc(&count, 4 * (size_t)n));
-        const char *bsel = getenv("LJ_BUILDER");       // "lbvh" keeps the plain radix tree; default PLOC
-        if (bsel && bsel[0] == 'l') {
+        if (lbvh) {
             k_radix_tree<<<G, B>>>(n, keys2, left, right, par_i, par_l);
             CK(cudaGetLastError());
             k_fit<<<G, B>>>(n, vals2, prim_lo, prim_hi, left, right, par_i, par_l, flags, node_lo, node_hi);
@@ -872,6 +900,7 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     out.num_bvh8 = h_info[2];
     out.num_slots8 = h_info[3];
     out.levels8 = h_info[7];
+    if (pt.on) fprintf(stderr, "[bvh]   8-wide tree: %d nodes, %d levels\n", out.num_bvh8, out.levels8);
     if (out.levels8 > 128) { snprintf(err, 256, "bvh8 collapse did not terminate"); return -1; }
     if (out.num_slots8 != n) { snprintf(err, 256, "bvh8 collapse lost primitives: %d of %d", out.num_slots8, n); return -1; }
     return 0;

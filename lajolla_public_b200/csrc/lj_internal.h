@@ -40,6 +40,7 @@ struct lj_scene {
     lj_stats build_stats;
     bool kind_present[LJ_MAT_KIND_COUNT];   // material kinds the scene uses (one shade launch per kind)
     bool grid_media;                        // any heterogeneous medium (the tracking kernels run)
+    bool media_grey;                        // every medium has equal channels everywhere (one-channel tracking, lj_volpath.cuh)
     std::vector<lj_scene *> replicas;       // multi-device contexts: one scene per device (this object is only the handle)
 };
 

@@ -264,40 +264,80 @@ LJ_D d3 vol_path_tracing_2(const DScene &sc, int x, int y, Pcg32 &rng, RayCounte
 // Tracking loops in begin / step form, so that the per-lane integrator (run to completion) and the
 // wavefront tracking kernel (lj_volwave.cu: one collision per lane per warp iteration, finished lanes
 // refilled) execute the very same arithmetic.
-struct TrackState { d3 majorant; double maj_c, accum_t; int channel, iteration; bool active; };
+//
+// The steps are written over a spectrum type S: d3 (the reference's Spectrum), or double for a GREY scene — every
+// medium has equal channels at every point (media_all_grey).  Then the three channels of every quantity of the loops
+// are one number produced by one sequence of operations, and computing a single channel gives the reference's bits
+// at a third of the arithmetic (one exp instead of three, no per-channel divisions).
+LJ_D d3 sp_exp(d3 a) { return exp3(a); }
+LJ_D double sp_exp(double a) { return exp(a); }
+LJ_D double sp_max(d3 a) { return max3(a); }
+LJ_D double sp_max(double a) { return a; }
+LJ_D double sp_comp(d3 a, int c) { return comp(a, c); }
+LJ_D double sp_comp(double a, int) { return a; }
+LJ_D d3 sp_div(d3 a, double s) { return a / s; }
+LJ_D double sp_div(double a, double s) { double inv = 1.0 / s; return a * inv; }      // one channel of `d3 / double` (vector.h:193-197)
 
-LJ_D void track_begin(const DScene &sc, const lj_medium &media, const Ray &ray, Pcg32 &rng, TrackState &ts) {
-    ts.majorant = medium_majorant(sc, media, ray);
+LJ_D bool medium_is_grey(const lj_medium &m) {
+    if (m.kind == LJ_MEDIUM_HOMOGENEOUS)
+        return m.sigma_a[0] == m.sigma_a[1] && m.sigma_a[0] == m.sigma_a[2] && m.sigma_s[0] == m.sigma_s[1] && m.sigma_s[0] == m.sigma_s[2];
+    return volume_is_grey(m.density) && volume_is_grey(m.albedo) &&
+           (m.density.kind == LJ_VOLUME_CONSTANT || (m.density.max_data[0] == m.density.max_data[1] && m.density.max_data[0] == m.density.max_data[2]));
+}
+template <typename S> LJ_D S medium_majorant_t(const DScene &sc, const lj_medium &m, const Ray &ray) {
+    if constexpr (sizeof(S) == sizeof(d3)) return medium_majorant(sc, m, ray);
+    else {      // channel 0 of medium_majorant
+        if (m.kind == LJ_MEDIUM_HOMOGENEOUS) return m.sigma_a[0] + m.sigma_s[0];
+        if (!volume_intersect(m.density, ray)) return 0.0;
+        if (m.density.kind == LJ_VOLUME_CONSTANT) return m.density.value[0];
+        return m.density.scale * m.density.max_data[0];
+    }
+}
+LJ_D void medium_sigma_sa(const DScene &sc, const lj_medium &m, d3 p, double &sigma_s, double &sigma_a) {    // channel 0 of the d3 overload
+    if (m.kind == LJ_MEDIUM_HOMOGENEOUS) { sigma_s = m.sigma_s[0]; sigma_a = m.sigma_a[0]; return; }
+    const double density = volume_lookup_grey(sc, m.density, p);
+    const double albedo = volume_lookup_grey(sc, m.albedo, p);
+    sigma_s = density * albedo;
+    sigma_a = density * (1.0 - albedo);
+}
+
+template <typename S> struct TrackStateT { S majorant; double maj_c, accum_t; int channel, iteration; bool active; };
+typedef TrackStateT<d3> TrackState;
+
+template <typename S>
+LJ_D void track_begin(const DScene &sc, const lj_medium &media, const Ray &ray, Pcg32 &rng, TrackStateT<S> &ts) {
+    ts.majorant = medium_majorant_t<S>(sc, media, ray);
     double u = pcg_real(rng);
     ts.channel = clampi((int)(u * 3), 0, 2);
     ts.accum_t = 0;
     ts.iteration = 0;
-    ts.maj_c = comp(ts.majorant, ts.channel);
+    ts.maj_c = sp_comp(ts.majorant, ts.channel);
     ts.active = !(ts.maj_c <= 0) && !(ts.iteration >= sc.options.max_null_collisions);
 }
 
 // One iteration of the NEE ratio-tracking loop (vol_path_tracing.h:364-408).
-LJ_D void ratio_track_step(const DScene &sc, const lj_medium &media, d3 p, d3 dir_light, double next_t, Pcg32 &rng, TrackState &ts,
-                           d3 &transmittance_light, d3 &p_trans_nee, d3 &p_trans_dir) {
-    const d3 majorant = ts.majorant;
+template <typename S>
+LJ_D void ratio_track_step(const DScene &sc, const lj_medium &media, d3 p, d3 dir_light, double next_t, Pcg32 &rng, TrackStateT<S> &ts,
+                           S &transmittance_light, S &p_trans_nee, S &p_trans_dir) {
+    const S majorant = ts.majorant;
     double t = -log(1 - pcg_real(rng)) / ts.maj_c;
     double dt = next_t - ts.accum_t;
     { const double s_ = ts.accum_t + t; ts.accum_t = (next_t < s_) ? next_t : s_; }   // std::min(accum_t + t, next_t)
     if (t < dt) {
         d3 pos = p + dir_light * ts.accum_t;
-        d3 sigma_s, sigma_a;
+        S sigma_s, sigma_a;
         medium_sigma_sa(sc, media, pos, sigma_s, sigma_a);
-        d3 sigma_t = sigma_s + sigma_a;
-        d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
-        d3 real_prob = sigma_t / majorant;
-        d3 e = exp3(-majorant * t);
-        double mx = max3(majorant);
-        transmittance_light = transmittance_light * (e * sigma_n / mx);
-        p_trans_nee = p_trans_nee * (e * majorant / mx);
-        p_trans_dir = p_trans_dir * (e * majorant * (1.0 - real_prob) / mx);
-        if (max3(transmittance_light) <= 0) { ts.active = false; return; }
+        S sigma_t = sigma_s + sigma_a;
+        S sigma_n = majorant * (1.0 - sigma_t / majorant);
+        S real_prob = sigma_t / majorant;
+        S e = sp_exp(-majorant * t);
+        double mx = sp_max(majorant);
+        transmittance_light = transmittance_light * sp_div(e * sigma_n, mx);
+        p_trans_nee = p_trans_nee * sp_div(e * majorant, mx);
+        p_trans_dir = p_trans_dir * sp_div(e * majorant * (1.0 - real_prob), mx);
+        if (sp_max(transmittance_light) <= 0) { ts.active = false; return; }
     } else {
-        d3 e = exp3(-majorant * dt);
+        S e = sp_exp(-majorant * dt);
         transmittance_light = transmittance_light * e;
         p_trans_nee = p_trans_nee * e;
         p_trans_dir = p_trans_dir * e;
@@ -317,34 +357,35 @@ LJ_D void ratio_track_segment(const DScene &sc, const lj_medium &media, const Ra
 
 // One iteration of the free-flight (delta tracking) loop (vol_path_tracing.h:565-621).  Sets `scatter`
 // and moves ray.org on a real collision or when the surface is reached.
-LJ_D void free_flight_step(const DScene &sc, const lj_medium &media, Ray &ray, double t_hit, d3 hit_position, Pcg32 &rng, TrackState &ts,
-                           d3 &transmittance, d3 &trans_dir_pdf, d3 &trans_nee_pdf, bool &scatter) {
-    const d3 majorant = ts.majorant;
+template <typename S>
+LJ_D void free_flight_step(const DScene &sc, const lj_medium &media, Ray &ray, double t_hit, d3 hit_position, Pcg32 &rng, TrackStateT<S> &ts,
+                           S &transmittance, S &trans_dir_pdf, S &trans_nee_pdf, bool &scatter) {
+    const S majorant = ts.majorant;
     double t = -log(1 - pcg_real(rng)) / ts.maj_c;
     double dt = t_hit - ts.accum_t;
     { const double s_ = ts.accum_t + t; ts.accum_t = (t_hit < s_) ? t_hit : s_; }
     if (t < dt) {
         d3 p = ray.org + ray.dir * ts.accum_t;
-        d3 sigma_s, sigma_a;
+        S sigma_s, sigma_a;
         medium_sigma_sa(sc, media, p, sigma_s, sigma_a);
-        d3 sigma_t = sigma_s + sigma_a;
-        d3 sigma_n = majorant * (1.0 - sigma_t / majorant);
-        d3 real_prob = sigma_t / majorant;
-        d3 e = exp3(-majorant * t);
-        double mx = max3(majorant);
-        if (pcg_real(rng) < comp(real_prob, ts.channel)) {
-            transmittance = transmittance * (e / mx);
-            trans_dir_pdf = trans_dir_pdf * (e * majorant * real_prob / mx);
+        S sigma_t = sigma_s + sigma_a;
+        S sigma_n = majorant * (1.0 - sigma_t / majorant);
+        S real_prob = sigma_t / majorant;
+        S e = sp_exp(-majorant * t);
+        double mx = sp_max(majorant);
+        if (pcg_real(rng) < sp_comp(real_prob, ts.channel)) {
+            transmittance = transmittance * sp_div(e, mx);
+            trans_dir_pdf = trans_dir_pdf * sp_div(e * majorant * real_prob, mx);
             ray.org = p;
             scatter = true;
             ts.active = false; return;
         } else {
-            transmittance = transmittance * (e * sigma_n / mx);
-            trans_dir_pdf = trans_dir_pdf * (e * majorant * (1.0 - real_prob) / mx);
-            trans_nee_pdf = trans_nee_pdf * (e * majorant / mx);
+            transmittance = transmittance * sp_div(e * sigma_n, mx);
+            trans_dir_pdf = trans_dir_pdf * sp_div(e * majorant * (1.0 - real_prob), mx);
+            trans_nee_pdf = trans_nee_pdf * sp_div(e * majorant, mx);
         }
     } else {
-        d3 e = exp3(-majorant * dt);
+        S e = sp_exp(-majorant * dt);
         transmittance = transmittance * e;
         trans_dir_pdf = trans_dir_pdf * e;
         trans_nee_pdf = trans_nee_pdf * e;

@@ -25,6 +25,9 @@
 #ifndef LJ_VOL_TRACK_MIN_BLOCKS
 #define LJ_VOL_TRACK_MIN_BLOCKS 1
 #endif
+#ifndef LJ_VOL_TRACK_GREY_MIN_BLOCKS
+#define LJ_VOL_TRACK_GREY_MIN_BLOCKS 1
+#endif
 #ifndef LJ_VOL_MAIN_MIN_BLOCKS
 #define LJ_VOL_MAIN_MIN_BLOCKS 1
 #endif
@@ -209,8 +212,21 @@ LJ_D int tracked_medium(const DScene &sc, int medium) {
     return (medium != -1 && sc.media[medium].kind == LJ_MEDIUM_HETEROGENEOUS) ? medium : -1;
 }
 
-template <bool NEE>
-__global__ void __launch_bounds__(128, LJ_VOL_TRACK_MIN_BLOCKS) k_vol_track(DScene sc, VolPool vp, int n_upper, int refill_below, int budget, int min_items, int parity) {
+// GREY: every medium of the scene has equal channels everywhere (lj_scene::media_grey), so every spectrum of the loops has
+// three equal channels: they are carried and computed as ONE double (see lj_volpath.cuh) and written back replicated.
+template <bool GREY> struct TrackSpectrum { typedef d3 type; };
+template <> struct TrackSpectrum<true> { typedef double type; };
+LJ_D d3 spread3(d3 a) { return a; }
+LJ_D d3 spread3(double a) { return mk3(a); }
+LJ_D void narrow3(d3 a, d3 &out) { out = a; }
+LJ_D void narrow3(d3 a, double &out) {
+    if (!(a.x == a.y && a.x == a.z)) __trap();      // a coloured spectrum in a scene flagged grey: never silently wrong
+    out = a.x;
+}
+
+template <bool NEE, bool GREY>
+__global__ void __launch_bounds__(128, GREY ? LJ_VOL_TRACK_GREY_MIN_BLOCKS : LJ_VOL_TRACK_MIN_BLOCKS) k_vol_track(DScene sc, VolPool vp, int n_upper, int refill_below, int budget, int min_items, int parity) {
+    typedef typename TrackSpectrum<GREY>::type S;
     // work = the segments suspended by the previous launch, then the fresh ones from the extend stage
     const int *q_cont = NEE ? vp.q_cont_nee[parity] : vp.q_cont_main[parity];
     int *q_susp = NEE ? vp.q_cont_nee[parity ^ 1] : vp.q_cont_main[parity ^ 1];
@@ -224,26 +240,28 @@ __global__ void __launch_bounds__(128, LJ_VOL_TRACK_MIN_BLOCKS) k_vol_track(DSce
     if (n < min_items) budget = 0x7fffffff;
     int *q_ready = NEE ? vp.q_nee_ready : vp.q_main_ready;
     int item = -1, slot = -1, medium = -1, steps = 0; bool exhausted = false;     // medium = -1: nothing to track for this item
-    TrackState ts; ts.active = false;
+    TrackStateT<S> ts; ts.active = false;
     Pcg32 rng; rng.state = 0; rng.inc = 1;
     Ray ray = make_ray(mk3(0.0), mk3(0.0), 0, 0);       // main ray, or the shadow segment
     double t_end = 0; d3 hit_position = mk3(0.0);
-    d3 A = mk3(1.0), Bv = mk3(1.0), Cv = mk3(1.0);      // main: transmittance, dir pdf, nee pdf; NEE: T_light, p_trans_nee, p_trans_dir
+    S A, Bv, Cv;                                        // main: transmittance, dir pdf, nee pdf; NEE: T_light, p_trans_nee, p_trans_dir
+    narrow3(mk3(1.0), A); narrow3(mk3(1.0), Bv); narrow3(mk3(1.0), Cv);
     bool scatter = false;
     while (true) {
         const bool running = item >= 0 && ts.active && steps < budget;
         if (item >= 0 && !running) {                    // retire: finished -> ready queue, out of budget -> suspended queue
             if (medium != -1) {
                 VolTrack tr;
+                const d3 A3 = spread3(A), B3 = spread3(Bv), C3 = spread3(Cv), mj3 = spread3(ts.majorant);
                 if (NEE) {
                     VolNee *ne = &vp.nee[slot];
-                    ne->ax = A.x; ne->ay = A.y; ne->az = A.z; ne->bx = Bv.x; ne->by = Bv.y; ne->bz = Bv.z; ne->ex = Cv.x; ne->ey = Cv.y; ne->ez = Cv.z;
+                    ne->ax = A3.x; ne->ay = A3.y; ne->az = A3.z; ne->bx = B3.x; ne->by = B3.y; ne->bz = B3.z; ne->ex = C3.x; ne->ey = C3.y; ne->ez = C3.z;
                     tr.tx = tr.ty = tr.tz = tr.dx = tr.dy = tr.dz = tr.nx = tr.ny = tr.nz = 0; tr.ox = tr.oy = tr.oz = 0;
                 } else {
-                    tr.tx = A.x; tr.ty = A.y; tr.tz = A.z; tr.dx = Bv.x; tr.dy = Bv.y; tr.dz = Bv.z; tr.nx = Cv.x; tr.ny = Cv.y; tr.nz = Cv.z;
+                    tr.tx = A3.x; tr.ty = A3.y; tr.tz = A3.z; tr.dx = B3.x; tr.dy = B3.y; tr.dz = B3.z; tr.nx = C3.x; tr.ny = C3.y; tr.nz = C3.z;
                     tr.ox = ray.org.x; tr.oy = ray.org.y; tr.oz = ray.org.z;
                 }
-                tr.mjx = ts.majorant.x; tr.mjy = ts.majorant.y; tr.mjz = ts.majorant.z; tr.accum_t = ts.accum_t;
+                tr.mjx = mj3.x; tr.mjy = mj3.y; tr.mjz = mj3.z; tr.accum_t = ts.accum_t;
                 tr.scatter = scatter ? 1 : 0; tr.channel = ts.channel; tr.iteration = ts.iteration; tr.pad0 = 0;
                 if (!NEE || ts.active) vp.track[slot] = tr;
                 vp.path[slot].rng = rng.state;
@@ -267,20 +285,20 @@ __global__ void __launch_bounds__(128, LJ_VOL_TRACK_MIN_BLOCKS) k_vol_track(DSce
                 ray = make_ray(pos, dir_light, sc.eps, (1 - sc.eps) * distance(pos, p_prime));
                 t_end = distance(pos, p_prime);
                 if (hr.geom >= 0) t_end = distance(pos, ray.org + ray.dir * (double)hr.t);      // |p - shadow_vertex.position|
-                A = mk3(ne.ax, ne.ay, ne.az); Bv = mk3(ne.bx, ne.by, ne.bz); Cv = mk3(ne.ex, ne.ey, ne.ez);
+                narrow3(mk3(ne.ax, ne.ay, ne.az), A); narrow3(mk3(ne.bx, ne.by, ne.bz), Bv); narrow3(mk3(ne.ex, ne.ey, ne.ez), Cv);
             } else {
                 const HitRec hr = vp.hit[slot];
                 medium = tracked_medium(sc, pp->medium);
                 ray = make_ray(mk3(pp->ox, pp->oy, pp->oz), mk3(pp->dx, pp->dy, pp->dz), sc.eps, INFINITY);
                 t_end = INFINITY; hit_position = mk3(0.0);
                 if (hr.geom >= 0) { hit_position = ray.org + ray.dir * (double)hr.t; t_end = distance(hit_position, ray.org); }
-                A = mk3(1.0); Bv = mk3(1.0); Cv = mk3(1.0);
+                narrow3(mk3(1.0), A); narrow3(mk3(1.0), Bv); narrow3(mk3(1.0), Cv);
             }
             if (resumed) {
                 const VolTrack tr = vp.track[slot];
-                if (!NEE) { A = mk3(tr.tx, tr.ty, tr.tz); Bv = mk3(tr.dx, tr.dy, tr.dz); Cv = mk3(tr.nx, tr.ny, tr.nz); }
-                ts.majorant = mk3(tr.mjx, tr.mjy, tr.mjz); ts.accum_t = tr.accum_t; ts.channel = tr.channel; ts.iteration = tr.iteration;
-                ts.maj_c = comp(ts.majorant, ts.channel); ts.active = true;
+                if (!NEE) { narrow3(mk3(tr.tx, tr.ty, tr.tz), A); narrow3(mk3(tr.dx, tr.dy, tr.dz), Bv); narrow3(mk3(tr.nx, tr.ny, tr.nz), Cv); }
+                narrow3(mk3(tr.mjx, tr.mjy, tr.mjz), ts.majorant); ts.accum_t = tr.accum_t; ts.channel = tr.channel; ts.iteration = tr.iteration;
+                ts.maj_c = sp_comp(ts.majorant, ts.channel); ts.active = true;
             } else if (medium != -1) track_begin(sc, sc.media[medium], ray, rng, ts);
         }
         if (!__ballot_sync(0xffffffffu, item >= 0)) break;
@@ -629,6 +647,7 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     const long long npix = (long long)rl.width * rl.height;
     const int nsamp = rl.s_end - rl.s_begin;
     const bool grid_media = s->grid_media;      // any heterogeneous medium -> run the tracking kernels
+    const bool media_grey = s->media_grey && !getenv("LJ_NO_GREY_TRACK");      // every medium has equal channels: one-channel tracking
     // slots in flight: grid media want many (the iteration count, not the arithmetic, bounds them: each iteration
     // waits for its slowest tracking chain), homogeneous scenes run best when the records stay close to L2 size
     long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (grid_media ? (8LL << 20) : (1LL << 20));
@@ -691,8 +710,13 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
         // with segments suspended from earlier launches more than `upper` slots may be in the tracking queues
         const int track_upper = exact ? upper + n_cont : capacity;
         if (grid_media) {
-            k_vol_track<false><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
-            k_vol_track<true><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
+            if (media_grey) {
+                k_vol_track<false, true><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
+                k_vol_track<true, true><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
+            } else {
+                k_vol_track<false, false><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
+                k_vol_track<true, false><<<grid_for(track_upper, trace_grid_cap), 128>>>(d, vp, track_upper, track_refill, track_budget, track_min_items, parity);
+            }
             k_vol_main<<<grid_for(track_upper, stage_grid_cap), 128>>>(d, vp, track_upper, vp.q_main_ready, VT_MAIN_READY);
             k_vol_nee<<<grid_for(track_upper, stage_grid_cap), 128>>>(d, vp, track_upper, vp.q_nee_ready, VT_NEE_READY);
         } else {
