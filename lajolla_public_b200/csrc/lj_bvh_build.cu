@@ -405,7 +405,7 @@ __global__ void k_ploc_compact(const int *m_ptr, int m_upper, int *m_next, const
 struct PlocBufs { int *cid[2], *cc[2]; float4 *clo[2], *chi[2]; };
 __global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int *lpos, unsigned long long *chunk_sums, int *counter,
                                                         int *left, int *right, int *count, float4 *node_lo, float4 *node_hi,
-                                                        const int radius, const int stop_at) {
+                                                        const int radius, const int stop_at, unsigned long long *dbg /* LJ_BVH_TRACE: phase time stamps */) {
     namespace cg = cooperative_groups;
     cg::grid_group grid = cg::this_grid();
     __shared__ float4 slo[PLOC_B + 2 * PLOC_RMAX], shi[PLOC_B + 2 * PLOC_RMAX];
@@ -414,9 +414,13 @@ __global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int
     const int tid = threadIdx.x, lane = tid & 31, w = tid >> 5;
     int m = counter[1], next_id = counter[0], cur = 0, rounds = 0;
     bool stuck = false;
+    auto stamp = [&](int phase) {
+        if (dbg && blockIdx.x == 0 && tid == 0 && rounds < 64) { unsigned long long t; asm volatile("mov.u64 %0, %%globaltimer;" : "=l"(t)); dbg[rounds * 4 + phase] = t; }
+    };
     while (m > stop_at) {
         const int chunks = (m + PLOC_B - 1) / PLOC_B;
         const float4 *clo = b.clo[cur], *chi = b.chi[cur];
+        stamp(0);
         // ---- A: nearest neighbours ----
         // T = 2^k threads per cluster once the grid has spare threads (as in k_ploc_tail): a block searches for PLOC_B / T
         // clusters, each thread takes every T-th candidate, the (area, index) minimum is the sequential scan's result
@@ -451,6 +455,7 @@ __global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int
             if (i < m && sub == 0) nn[i] = bj;
         }
         grid.sync();
+        stamp(1);
         // ---- B: merge decisions, scan inside the chunk ----
         for (int c = blockIdx.x; c < chunks; c += gridDim.x) {
             const int i = c * PLOC_B + tid;
@@ -474,6 +479,7 @@ __global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int
             if (tid == 0) chunk_sums[c] = (unsigned long long)(total & 0xffff) | ((unsigned long long)(total >> 16) << 32);
         }
         grid.sync();
+        stamp(2);
         // ---- C: global positions, node creation, compaction into the other buffer ----
         const int *cid = b.cid[cur], *cc = b.cc[cur];
         int *cid2 = b.cid[cur ^ 1], *cc2 = b.cc[cur ^ 1];
@@ -527,6 +533,7 @@ __global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int
         }
         const int m_new = (int)(tot & 0xffffffffu);
         next_id += (int)(tot >> 32);
+        stamp(3);
         rounds++;
         cur ^= 1;
         if (m_new >= m || m_new < 1 || rounds > 4096) { stuck = true; break; }     // uniform over the grid
@@ -546,6 +553,9 @@ __global__ void __launch_bounds__(PLOC_B) k_ploc_rounds(PlocBufs b, int *nn, int
 // clusters in shared memory and block-wide scans instead of a launch sequence + a blocking read-back per round.  The
 // tail used to be most of the build's ~600 launches (66 k primitives: ~9 rounds get below 1024 clusters, ~60 follow).
 constexpr int PLOC_TAIL = 1024;
+// the cooperative rounds hand over at this many clusters: a round costs them ~13 us whatever is left (three grid barriers),
+// the one-block tail ~18 us per round at 1024 clusters (200 candidates per thread on ONE SM) but 2-5 us below 256
+constexpr int PLOC_COOP_STOP = 256;
 __device__ __forceinline__ int block_scan_excl_1024(int v, int *warp_sums, int *total) {
     const int lane = threadIdx.x & 31, w = threadIdx.x >> 5;
     int x = v;
@@ -690,9 +700,24 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
             CK(lj_malloc(&chunk_sums, 8 * (size_t)chunks));
             PlocBufs bufs;
             for (int b = 0; b < 2; b++) { bufs.cid[b] = cid[b]; bufs.cc[b] = cc[b]; bufs.clo[b] = clo[b]; bufs.chi[b] = chi[b]; }
-            int *lpos = valid; int stop_at = PLOC_TAIL; int rad = radius;
-            void *args[] = {&bufs, &nn, &lpos, &chunk_sums, &counter, &left, &right, &count, &node_lo, &node_hi, &rad, &stop_at};
+            int *lpos = valid; int stop_at = PLOC_COOP_STOP; int rad = radius;
+            if (const char *e = getenv("LJ_PLOC_STOP")) { int v = atoi(e); if (v >= 1 && v <= PLOC_TAIL) stop_at = v; }
+            unsigned long long *dbg = nullptr;
+            if (trace) { CK(lj_malloc(&dbg, 8 * 256)); CK(cudaMemsetAsync(dbg, 0, 8 * 256, 0)); }
+            void *args[] = {&bufs, &nn, &lpos, &chunk_sums, &counter, &left, &right, &count, &node_lo, &node_hi, &rad, &stop_at, &dbg};
             CK(cudaLaunchCooperativeKernel((const void *)k_ploc_rounds, dim3(grid), dim3(PLOC_B), args, 0, 0));
+            if (trace) {
+                unsigned long long h[256];
+                CK(cudaMemcpy(h, dbg, sizeof h, cudaMemcpyDeviceToHost));
+                lj_free(dbg);
+                double a = 0, b2 = 0, c = 0, nxt = 0; int nr = 0;
+                for (int r = 0; r < 64 && h[4 * r + 3]; r++, nr++) {
+                    a += (double)(h[4 * r + 1] - h[4 * r]); b2 += (double)(h[4 * r + 2] - h[4 * r + 1]); c += (double)(h[4 * r + 3] - h[4 * r + 2]);
+                    if (r + 1 < 64 && h[4 * r + 4]) nxt += (double)(h[4 * r + 4] - h[4 * r + 3]);
+                }
+                if (nr) fprintf(stderr, "[bvh]   PLOC rounds, block 0, us per round: search + barrier %.2f, decide + barrier %.2f, compact %.2f, closing barrier %.2f (grid %d)\n",
+                                a / nr * 1e-3, b2 / nr * 1e-3, c / nr * 1e-3, nxt / nr * 1e-3, grid);
+            }
         }
         std::chrono::steady_clock::time_point t_a, t_b;
         int h[4] = {0, 0, 0, 0};
@@ -839,12 +864,11 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
     CK(lj_malloc(&vals, 4 * (size_t)n)); CK(lj_malloc(&vals2, 4 * (size_t)n));
     k_morton<<<G, B>>>(n, prim_lo, prim_hi, bounds, keys, vals);
     CK(cudaGetLastError());
-    // PLOC only needs the primitives in an order that keeps neighbours in space close in the array: up to 2^20 primitives
-    // the top 32 of the 63 code bits do that (4 radix passes instead of 8; equal prefixes stay in input order, the sort is
-    // stable).  The radix-tree builder reads the sorted codes themselves and gets all 63.  LJ_SORT_BITS overrides.
+    // LJ_SORT_BITS: sort on the top bits of the code only (fewer radix passes).  Measured and not adopted: 32 bits take
+    // 0.2 ms off sponza's sort and cost 5 % of its traversal time (extend 74.4 -> 78.4 ms), profiles/r02_experiments.md.
     const char *bsel = getenv("LJ_BUILDER");       // "lbvh" keeps the plain radix tree; default PLOC
     const bool lbvh = bsel && bsel[0] == 'l';
-    int sort_bits = (lbvh || n > (1 << 20)) ? 63 : 32;
+    int sort_bits = 63;
     if (const char *e = getenv("LJ_SORT_BITS")) { int v = atoi(e); if (v >= 8 && v <= 63 && !lbvh) sort_bits = v; }
     size_t tmp_bytes = 0;
     CK(cub::DeviceRadixSort::SortPairs(nullptr, tmp_bytes, keys, keys2, vals, vals2, n, 63 - sort_bits, 63));
@@ -875,6 +899,29 @@ static int lj_bvh_build_refs(const BvhBuildInput &in, BvhBuildOutput &out, char 
             if (ploc_build(n, vals2, prim_lo, prim_hi, left, right, count, node_lo, node_hi, d_info, err) != 0) { free_temps(); return -1; }
         }
         pt.mark("PLOC");
+        if (pt.on) {
+            // id-independent fingerprint of the binary tree (the builders number their nodes differently): a node hashes
+            // its children's hashes in order, a leaf its sorted slot
+            std::vector<int> hl(n), hr(n); int hroot = 0;
+            CK(cudaMemcpy(hl.data(), left, 4 * (size_t)n, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(hr.data(), right, 4 * (size_t)n, cudaMemcpyDeviceToHost));
+            CK(cudaMemcpy(&hroot, d_info, 4, cudaMemcpyDeviceToHost));
+            std::vector<unsigned long long> hv(n, 0ull); std::vector<char> done(n, 0); std::vector<int> stk;
+            auto leaf_h = [](int c) { unsigned long long x = (unsigned long long)(unsigned)~c * 0x9E3779B97F4A7C15ull; return x ^ (x >> 29); };
+            stk.push_back(hroot);
+            while (!stk.empty()) {
+                const int x = stk.back();
+                const int l = hl[x], r = hr[x];
+                const bool lr = l < 0 || done[l], rr = r < 0 || done[r];
+                if (lr && rr) {
+                    const unsigned long long a = l < 0 ? leaf_h(l) : hv[l], b = r < 0 ? leaf_h(r) : hv[r];
+                    unsigned long long h = (a * 0xBF58476D1CE4E5B9ull) ^ ((b + 0x94D049BB133111EBull) * 0xD6E8FEB86659FD93ull);
+                    hv[x] = h ^ (h >> 31); done[x] = 1; stk.pop_back();
+                } else { if (!lr) stk.push_back(l); if (!rr) stk.push_back(r); }
+            }
+            fprintf(stderr, "[bvh]   binary tree fingerprint %016llx\n", hv[hroot]);
+            pt.mark("(fingerprint)");
+        }
         CK(lj_malloc(&out.bvh2, sizeof(Bvh2Node) * (size_t)(n - 1)));
         k_emit_bvh2<<<G, B>>>(n, left, right, node_lo, node_hi, out.bvh2);
         CK(cudaGetLastError());

@@ -35,7 +35,17 @@ LJ_HD d3 operator*(d3 a, double s) { return mk3(a.x * s, a.y * s, a.z * s); }
 LJ_HD d3 operator*(double s, d3 a) { return mk3(s * a.x, s * a.y, s * a.z); }
 // vector.h:193-197: division by a scalar is a multiplication by 1/s
 LJ_HD d3 operator/(d3 a, double s) { double inv = 1.0 / s; return mk3(a.x * inv, a.y * inv, a.z * inv); }
-LJ_HD d3 operator/(d3 a, d3 b) { return mk3(a.x / b.x, a.y / b.y, a.z / b.z); }
+// x / d for an x that is often exactly zero.  IEEE: (+-0) / d = +-0 with the sign of x xor d for every finite non-zero d,
+// which is what (+-0) * d gives, so the quotient is returned without dividing.  Worth a branch because CUDA's f64
+// division leaves its ~12-instruction fast path for a ~65-instruction subroutine whenever the numerator (or the
+// quotient) is zero or tiny: ncu showed that subroutine as 11 % of the Lambertian shade kernel's instructions (uv
+// partials of axis-aligned texture coordinates) and 18 % of the grid-medium tracker's (sigma_t = 0 in empty voxels),
+// run at 8-15 of 32 lanes.  Bit-identical by construction; profiles/r02_experiments.md.
+LJ_HD double div_z(double x, double d) {
+    const double ad = fabs(d);
+    return (x == 0.0 && ad > 0.0 && ad <= 1.7976931348623157e308) ? x * d : x / d;
+}
+LJ_HD d3 operator/(d3 a, d3 b) { return mk3(div_z(a.x, b.x), div_z(a.y, b.y), div_z(a.z, b.z)); }
 LJ_HD d3 &operator+=(d3 &a, d3 b) { a.x += b.x; a.y += b.y; a.z += b.z; return a; }
 LJ_HD d3 operator-(double s, d3 a) { return mk3(s - a.x, s - a.y, s - a.z); }
 

@@ -21,6 +21,7 @@
 
 LJ_D d3 exp3(d3 a) { return mk3(exp(a.x), exp(a.y), exp(a.z)); }   // spectrum.h:28-30
 LJ_D d3 load3f(const float *p, size_t i) { return mk3((double)__ldg(p + 3 * i), (double)__ldg(p + 3 * i + 1), (double)__ldg(p + 3 * i + 2)); }
+LJ_D d3 load3f4(const float4 *g4, size_t i) { const float4 t = __ldg(g4 + 2 * i); return mk3((double)t.x, (double)t.y, (double)t.z); }   // paired records: stride 2 float4
 // volume.h:68-80: the trilinear blend, terms added in the reference's order
 LJ_D d3 volume_blend(double scale, double dx, double dy, double dz, d3 v000, d3 v001, d3 v010, d3 v011, d3 v100, d3 v101, d3 v110, d3 v111) {
     return scale * (v000 * ((1 - dx) * (1 - dy) * (1 - dz)) +
@@ -89,7 +90,12 @@ LJ_D d3 volume_lookup(const DScene &sc, const lj_volume &v, d3 p) {
         return mk3(volume_blend_grey(sc.grid_f32 + v.data_offset, v.scale, dx, dy, dz, i000, i001, i010, i011, i100, i101, i110, i111));
     }
     d3 v000, v001, v010, v011, v100, v101, v110, v111;
-    if (v._pad == 3) {
+    if (v._pad == 8) {
+        // one half of a paired record (8 floats per voxel: density rgb, 0, albedo rgb, 0; _pad2 picks the half)
+        const float4 *g4 = (const float4 *)(sc.grid_f32 + v.data_offset) + v._pad2;
+        v000 = load3f4(g4, i000); v001 = load3f4(g4, i001); v010 = load3f4(g4, i010); v011 = load3f4(g4, i011);
+        v100 = load3f4(g4, i100); v101 = load3f4(g4, i101); v110 = load3f4(g4, i110); v111 = load3f4(g4, i111);
+    } else if (v._pad == 3) {
         const float *gf = sc.grid_f32 + v.data_offset;
         v000 = load3f(gf, i000); v001 = load3f(gf, i001); v010 = load3f(gf, i010); v011 = load3f(gf, i011);
         v100 = load3f(gf, i100); v101 = load3f(gf, i101); v110 = load3f(gf, i110); v111 = load3f(gf, i111);
@@ -145,8 +151,24 @@ LJ_D void medium_sigma_sa(const DScene &sc, const lj_medium &m, d3 p, d3 &sigma_
         sigma_a = mk3(m.sigma_a[0], m.sigma_a[1], m.sigma_a[2]);
         return;
     }
-    d3 density = volume_lookup(sc, m.density, p);
-    d3 albedo = volume_lookup(sc, m.albedo, p);
+    d3 density, albedo;
+    if (m.density._pad == 8) {
+        // density and albedo share their cells (paired records, lj_api.cu): one cell computation, 8 x 32 contiguous bytes;
+        // each grid's value is volume_lookup's (same corners, same weights, same blend, its own scale)
+        GridCell c;
+        if (!grid_cell(m.density, p, c)) { density = mk3(0.0); albedo = mk3(0.0); }
+        else {
+            const float4 *g4 = (const float4 *)(sc.grid_f32 + m.density.data_offset);
+            density = volume_blend(m.density.scale, c.dx, c.dy, c.dz, load3f4(g4, c.i000), load3f4(g4, c.i001), load3f4(g4, c.i010), load3f4(g4, c.i011),
+                                   load3f4(g4, c.i100), load3f4(g4, c.i101), load3f4(g4, c.i110), load3f4(g4, c.i111));
+            g4 += 1;
+            albedo = volume_blend(m.albedo.scale, c.dx, c.dy, c.dz, load3f4(g4, c.i000), load3f4(g4, c.i001), load3f4(g4, c.i010), load3f4(g4, c.i011),
+                                  load3f4(g4, c.i100), load3f4(g4, c.i101), load3f4(g4, c.i110), load3f4(g4, c.i111));
+        }
+    } else {
+        density = volume_lookup(sc, m.density, p);
+        albedo = volume_lookup(sc, m.albedo, p);
+    }
     sigma_s = density * albedo;
     sigma_a = density * (1.0 - albedo);
 }
@@ -277,6 +299,8 @@ LJ_D double sp_comp(d3 a, int c) { return comp(a, c); }
 LJ_D double sp_comp(double a, int) { return a; }
 LJ_D d3 sp_div(d3 a, double s) { return a / s; }
 LJ_D double sp_div(double a, double s) { double inv = 1.0 / s; return a * inv; }      // one channel of `d3 / double` (vector.h:193-197)
+LJ_D d3 sp_quot(d3 a, d3 b) { return a / b; }                                        // d3 / d3: true division per channel
+LJ_D double sp_quot(double a, double b) { return div_z(a, b); }
 
 LJ_D bool medium_is_grey(const lj_medium &m) {
     if (m.kind == LJ_MEDIUM_HOMOGENEOUS)
@@ -328,8 +352,8 @@ LJ_D void ratio_track_step(const DScene &sc, const lj_medium &media, d3 p, d3 di
         S sigma_s, sigma_a;
         medium_sigma_sa(sc, media, pos, sigma_s, sigma_a);
         S sigma_t = sigma_s + sigma_a;
-        S sigma_n = majorant * (1.0 - sigma_t / majorant);
-        S real_prob = sigma_t / majorant;
+        S real_prob = sp_quot(sigma_t, majorant);       // sigma_t / majorant; zero in empty voxels: div_z
+        S sigma_n = majorant * (1.0 - real_prob);
         S e = sp_exp(-majorant * t);
         double mx = sp_max(majorant);
         transmittance_light = transmittance_light * sp_div(e * sigma_n, mx);
@@ -369,8 +393,8 @@ LJ_D void free_flight_step(const DScene &sc, const lj_medium &media, Ray &ray, d
         S sigma_s, sigma_a;
         medium_sigma_sa(sc, media, p, sigma_s, sigma_a);
         S sigma_t = sigma_s + sigma_a;
-        S sigma_n = majorant * (1.0 - sigma_t / majorant);
-        S real_prob = sigma_t / majorant;
+        S real_prob = sp_quot(sigma_t, majorant);       // sigma_t / majorant; zero in empty voxels: div_z
+        S sigma_n = majorant * (1.0 - real_prob);
         S e = sp_exp(-majorant * t);
         double mx = sp_max(majorant);
         if (pcg_real(rng) < sp_comp(real_prob, ts.channel)) {

@@ -23,7 +23,7 @@
 
 // resident blocks per SM the per-vertex and tracking kernels are compiled for (experiment knobs; 1 = no register cap)
 #ifndef LJ_VOL_TRACK_MIN_BLOCKS
-#define LJ_VOL_TRACK_MIN_BLOCKS 1
+#define LJ_VOL_TRACK_MIN_BLOCKS 3
 #endif
 #ifndef LJ_VOL_TRACK_GREY_MIN_BLOCKS
 #define LJ_VOL_TRACK_GREY_MIN_BLOCKS 1

@@ -61,3 +61,20 @@ def test_volpath_many_spp_same_streams(gpu, manifest, name, engine):
           f"{st.samples / st.render_ms * 1e-3:.2f} Msamples/s, {st.rays / st.render_ms * 1e-3:.1f} Mrays/s")
     assert frac >= 0.85
     assert abs(float(img.mean()) - float(ref.mean())) <= 0.02 * float(ref.mean())
+
+
+@pytest.mark.parametrize("name", ["hetvol", "hetvol_colored"])
+def test_grey_media_tracking_is_bit_identical(gpu, manifest, name, monkeypatch):
+    """Scenes whose media all have equal channels track ONE channel (lj_volpath.cuh, `sp_*` over double): the image must
+    be the three-channel kernels' image bit for bit (hetvol is grey; hetvol_colored is not and runs the same kernels twice)."""
+    from lajolla_public_b200 import RenderParams, RNG_SAMPLE_STREAMS, ENGINE_WAVEFRONT
+    d, e, scene = load(gpu, manifest, name)
+    rp = RenderParams(spp=4, rng_mode=RNG_SAMPLE_STREAMS, engine=ENGINE_WAVEFRONT)
+    monkeypatch.delenv("LJ_NO_GREY_TRACK", raising=False)
+    grey, st_g = scene.render(rp)
+    monkeypatch.setenv("LJ_NO_GREY_TRACK", "1")
+    full, st_f = scene.render(rp)
+    scene.close()
+    print(f"{name}: grey {st_g.render_ms:.2f} ms, three channels {st_f.render_ms:.2f} ms, rays {st_g.rays} vs {st_f.rays}")
+    assert st_g.rays == st_f.rays
+    assert np.array_equal(grey.view(np.uint32), full.view(np.uint32))
