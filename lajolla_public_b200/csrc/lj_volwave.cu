@@ -26,7 +26,7 @@
 #define LJ_VOL_TRACK_MIN_BLOCKS 3
 #endif
 #ifndef LJ_VOL_TRACK_GREY_MIN_BLOCKS
-#define LJ_VOL_TRACK_GREY_MIN_BLOCKS 1
+#define LJ_VOL_TRACK_GREY_MIN_BLOCKS 5
 #endif
 #ifndef LJ_VOL_MAIN_MIN_BLOCKS
 #define LJ_VOL_MAIN_MIN_BLOCKS 1
@@ -650,7 +650,7 @@ int lj_render_volwave(lj_scene *s, const RenderLaunch &rl, double *dev_sum, lj_s
     const bool media_grey = s->media_grey && !getenv("LJ_NO_GREY_TRACK");      // every medium has equal channels: one-channel tracking
     // slots in flight: grid media want many (the iteration count, not the arithmetic, bounds them: each iteration
     // waits for its slowest tracking chain), homogeneous scenes run best when the records stay close to L2 size
-    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (grid_media ? (8LL << 20) : (1LL << 20));
+    long long target = rl.p.paths_in_flight > 0 ? rl.p.paths_in_flight : (grid_media ? (16LL << 20) : (1LL << 20));
     // (a target just below a power of two of sample lanes is rounded UP: K is a power of two, see SlotMap)
     const SlotMap map = lj_make_slot_map(rl.width, rl.height, rl.s_begin, rl.s_end, rl.p.tile_rank, rl.p.tile_world, target + target / 2);
     if ((long long)map.npix_local * map.K > 0x3fffffffLL / 4) { lj_set_error("volumetric wavefront: pool too large"); return LJ_EINVAL; }
