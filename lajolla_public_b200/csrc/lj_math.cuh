@@ -38,9 +38,9 @@ LJ_HD d3 operator/(d3 a, double s) { double inv = 1.0 / s; return mk3(a.x * inv,
 // x / d for an x that is often exactly zero.  IEEE: (+-0) / d = +-0 with the sign of x xor d for every finite non-zero d,
 // which is what (+-0) * d gives, so the quotient is returned without dividing.  Worth a branch because CUDA's f64
 // division leaves its ~12-instruction fast path for a ~65-instruction subroutine whenever the numerator (or the
-// quotient) is zero or tiny: ncu showed that subroutine as 11 % of the Lambertian shade kernel's instructions (uv
-// partials of axis-aligned texture coordinates) and 18 % of the grid-medium tracker's (sigma_t = 0 in empty voxels),
-// run at 8-15 of 32 lanes.  Bit-identical by construction; profiles/r02_experiments.md.
+// quotient) is zero or tiny: ncu showed that subroutine as 18 % of the grid-medium tracker's instructions (sigma_t = 0 in
+// empty voxels), run at 8 of 32 lanes; hetvol_colored 31.0 -> 38.5 Msamples/s.  Bit-identical by construction;
+// profiles/r02_experiments.md (where it did NOT pay: the uv partials of lj_shading.cuh).
 LJ_HD double div_z(double x, double d) {
     const double ad = fabs(d);
     return (x == 0.0 && ad > 0.0 && ad <= 1.7976931348623157e308) ? x * d : x / d;

@@ -161,11 +161,13 @@ LJ_D ShadingInfo shading_info_mesh(const DScene &sc, const lj_shape &s, const Pa
     d2 duvds = uv2 - uv0;
     d2 duvdt = uv2 - uv1;
     double det = duvds.x * duvdt.y - duvdt.x * duvds.y;
-    // (axis-aligned texture coordinates make most of these numerators exactly zero: div_z, lj_math.cuh)
-    double dsdu = div_z(duvdt.y, det);
-    double dtdu = div_z(-duvds.y, det);
-    double dsdv = div_z(duvdt.x, det);
-    double dtdv = div_z(-duvds.x, det);
+    // (axis-aligned texture coordinates make most of these numerators exactly zero, which sends CUDA's f64 division into
+    // its slow-path subroutine; routing them through div_z (lj_math.cuh) removed 11 % of this kernel's instructions and
+    // made it 2 % SLOWER, 47.8 -> 48.7 ms per sponza step: it waits on loads, not on issue slots.  Left as plain divisions.)
+    double dsdu = duvdt.y / det;
+    double dtdu = -duvds.y / det;
+    double dsdv = duvdt.x / det;
+    double dtdv = -duvds.x / det;
     d3 dpdu, dpdv;
     if (fabs(det) > (double)1e-8f) {
         d3 dpds = p2 - p0;
@@ -229,7 +231,7 @@ LJ_D PathVertex make_vertex(const DScene &sc, const Ray &ray, const Hit &h, cons
     v.uv = si.uv;
     v.mean_curvature = si.mean_curvature;
     v.ray_radius = rd_transfer(rd, distance(ray.org, v.position));
-    v.uv_screen_size = div_z(v.ray_radius, si.inv_uv_size);
+    v.uv_screen_size = v.ray_radius / si.inv_uv_size;
     if (dot(v.geometry_normal, v.shading_frame.n) < 0) v.geometry_normal = -v.geometry_normal;
     return v;
 }

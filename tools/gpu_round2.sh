@@ -22,8 +22,8 @@ if [ $rc -eq 0 ]; then
   for k in extend shade shadow; do
     timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_wf_$k -s 6 -c 1 -o gpurun_out/${k}_full -f $NB > gpurun_out/ncu_full_$k.log 2>&1; echo "ncu $k rc=$?"
   done
-  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_vol_track -s 20 -c 1 -o gpurun_out/vol_track_full -f \
-      python tools/sweep_pool.py hetvol 8 8388608 > gpurun_out/ncu_full_track.log 2>&1; echo "ncu track rc=$?"
+  timeout 900 ncu --set full --clock-control none --import-source on -k regex:k_vol_track -s 2 -c 1 -o gpurun_out/vol_track_full -f \
+      python tools/sweep_pool.py hetvol 8 16777216 > gpurun_out/ncu_full_track.log 2>&1; echo "ncu track rc=$?"
 fi
 # the reports are too big to travel (gpurun_out is capped at 64 MiB): summarise them here, keep only the summaries
 mkdir -p gpurun_out/profiles_$TAG
