@@ -21,7 +21,9 @@
 #include <cstdlib>
 #include <algorithm>
 
-// resident blocks per SM the per-vertex and tracking kernels are compiled for (experiment knobs; 1 = no register cap)
+// resident blocks per SM the per-vertex and tracking kernels are compiled for (experiment knobs; 1 = no register cap).
+// Coloured tracker: 3 (168 registers, 40 B of spills) -- 2 blocks (212 registers): hetvol_colored 24.8 Msamples/s, 3: 39.6, 4 (128 registers,
+// 200 B of spills): 37.8.  Grey tracker: 5 (84-92 registers, no spills); 4 and 6 measure the same.
 #ifndef LJ_VOL_TRACK_MIN_BLOCKS
 #define LJ_VOL_TRACK_MIN_BLOCKS 3
 #endif

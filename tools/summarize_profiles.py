@@ -87,7 +87,7 @@ def full(tag, src, out):
         name = rep[:-8]
         with open(os.path.join(out, f"{tag}_{name}.md"), "w") as f:
             f.write(f"# {tag}: `ncu --set full --clock-control none` of one launch of `{short(d['Kernel Name'][0])}`\n\n")
-            what = ("`python tools/sweep_pool.py hetvol 8 8388608` (hetvol 768x576, 8 spp, volumetric wavefront engine); launch `-s 20 -c 1`"
+            what = ("`python tools/sweep_pool.py hetvol 8 16777216` (hetvol 768x576, 8 spp, volumetric wavefront engine); launch `-s 2 -c 1`"
                     if "track" in name else
                     "`python bench.py --steps 1 --warmup 1` (sponza 768x575, 64 spp, wavefront engine); a mid-render launch (`-s 6 -c 1`)")
             f.write(f"Captured inside {what}.\n\n| metric | value | unit |\n|---|---|---|\n")
