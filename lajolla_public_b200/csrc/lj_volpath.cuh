@@ -383,7 +383,7 @@ LJ_D void ratio_track_segment(const DScene &sc, const lj_medium &media, const Ra
 // and moves ray.org on a real collision or when the surface is reached.
 template <typename S>
 LJ_D void free_flight_step(const DScene &sc, const lj_medium &media, Ray &ray, double t_hit, d3 hit_position, Pcg32 &rng, TrackStateT<S> &ts,
-                           S &transmittance, S &trans_dir_pdf, S &trans_nee_pdf, bool &scatter) {
+                           S &transmittance, S &trans_dir_pdf, S &trans_nee_pdf, bool &scatter, bool *reached_surface = nullptr) {
     const S majorant = ts.majorant;
     double t = -log(1 - pcg_real(rng)) / ts.maj_c;
     double dt = t_hit - ts.accum_t;
@@ -413,7 +413,9 @@ LJ_D void free_flight_step(const DScene &sc, const lj_medium &media, Ray &ray, d
         transmittance = transmittance * e;
         trans_dir_pdf = trans_dir_pdf * e;
         trans_nee_pdf = trans_nee_pdf * e;
-        ray.org = hit_position;             // dt finite => a hit exists
+        // dt finite => a hit exists.  A caller that does not want to carry hit_position through its loop (the tracking
+        // kernel: six registers) passes a flag instead and moves the origin itself afterwards.
+        if (reached_surface) *reached_surface = true; else ray.org = hit_position;
         ts.active = false; return;
     }
     ts.iteration++;

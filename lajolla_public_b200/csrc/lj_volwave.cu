@@ -245,7 +245,8 @@ __global__ void __launch_bounds__(128, GREY ? LJ_VOL_TRACK_GREY_MIN_BLOCKS : LJ_
     TrackStateT<S> ts; ts.active = false;
     Pcg32 rng; rng.state = 0; rng.inc = 1;
     Ray ray = make_ray(mk3(0.0), mk3(0.0), 0, 0);       // main ray, or the shadow segment
-    double t_end = 0; d3 hit_position = mk3(0.0);
+    double t_end = 0;
+    bool reached = false;       // main rays: the free flight ended on the surface (its position is recomputed at retire time)
     S A, Bv, Cv;                                        // main: transmittance, dir pdf, nee pdf; NEE: T_light, p_trans_nee, p_trans_dir
     narrow3(mk3(1.0), A); narrow3(mk3(1.0), Bv); narrow3(mk3(1.0), Cv);
     bool scatter = false;
@@ -261,7 +262,12 @@ __global__ void __launch_bounds__(128, GREY ? LJ_VOL_TRACK_GREY_MIN_BLOCKS : LJ_
                     tr.tx = tr.ty = tr.tz = tr.dx = tr.dy = tr.dz = tr.nx = tr.ny = tr.nz = 0; tr.ox = tr.oy = tr.oz = 0;
                 } else {
                     tr.tx = A3.x; tr.ty = A3.y; tr.tz = A3.z; tr.dx = B3.x; tr.dy = B3.y; tr.dz = B3.z; tr.nx = C3.x; tr.ny = C3.y; tr.nz = C3.z;
-                    tr.ox = ray.org.x; tr.oy = ray.org.y; tr.oz = ray.org.z;
+                    d3 org = ray.org;
+                    if (reached) {              // ray.org = hit_position (vol_path_tracing.h:617), the expression of the fetch below
+                        const VolPath *pp = &vp.path[slot];
+                        org = mk3(pp->ox, pp->oy, pp->oz) + ray.dir * (double)vp.hit[slot].t;
+                    }
+                    tr.ox = org.x; tr.oy = org.y; tr.oz = org.z;
                 }
                 tr.mjx = mj3.x; tr.mjy = mj3.y; tr.mjz = mj3.z; tr.accum_t = ts.accum_t;
                 tr.scatter = scatter ? 1 : 0; tr.channel = ts.channel; tr.iteration = ts.iteration; tr.pad0 = 0;
@@ -292,8 +298,8 @@ __global__ void __launch_bounds__(128, GREY ? LJ_VOL_TRACK_GREY_MIN_BLOCKS : LJ_
                 const HitRec hr = vp.hit[slot];
                 medium = tracked_medium(sc, pp->medium);
                 ray = make_ray(mk3(pp->ox, pp->oy, pp->oz), mk3(pp->dx, pp->dy, pp->dz), sc.eps, INFINITY);
-                t_end = INFINITY; hit_position = mk3(0.0);
-                if (hr.geom >= 0) { hit_position = ray.org + ray.dir * (double)hr.t; t_end = distance(hit_position, ray.org); }
+                t_end = INFINITY; reached = false;
+                if (hr.geom >= 0) { const d3 hit_position = ray.org + ray.dir * (double)hr.t; t_end = distance(hit_position, ray.org); }
                 narrow3(mk3(1.0), A); narrow3(mk3(1.0), Bv); narrow3(mk3(1.0), Cv);
             }
             if (resumed) {
@@ -308,7 +314,7 @@ __global__ void __launch_bounds__(128, GREY ? LJ_VOL_TRACK_GREY_MIN_BLOCKS : LJ_
         while (true) {
             if (item >= 0 && ts.active && steps < budget) {
                 if (NEE) ratio_track_step(sc, sc.media[medium], ray.org, ray.dir, t_end, rng, ts, A, Bv, Cv);
-                else free_flight_step(sc, sc.media[medium], ray, t_end, hit_position, rng, ts, A, Bv, Cv, scatter);
+                else free_flight_step(sc, sc.media[medium], ray, t_end, ray.org, rng, ts, A, Bv, Cv, scatter, &reached);
                 steps += exhausted ? 1 : 0;
             }
             if (__popc(__ballot_sync(0xffffffffu, item >= 0 && ts.active && steps < budget)) < stop_below) break;
