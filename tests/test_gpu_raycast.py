@@ -61,3 +61,35 @@ def test_bvh8_matches_bvh2(gpu, name):
     assert np.array_equal(o2["t"], o8["t"])
     # occlusion agrees with closest hit: occluded <=> a hit exists within (tnear, tfar]
     assert np.array_equal(np.isneginf(o8["t"]), h8["geom_id"] >= 0)
+
+
+@pytest.mark.parametrize("name", ["cbox", "sponza", "matpreview"])
+def test_cooperative_build_equals_launch_sequence(gpu, name, monkeypatch):
+    """The cooperative PLOC / collapse kernels (lj_bvh_build.cu, lj_bvh8_build.cu: the default) and the launch-sequence
+    builders behind LJ_PLOC_COOP=0 / LJ_BVH8_COOP=0 implement the same algorithm: same node count, same hits bit for bit
+    (closest hit and occlusion), also with the hand-over to the one-block tail moved."""
+    d = fixture_dir(name)
+    if d is None:
+        pytest.skip("fixture missing")
+    blob = os.path.join(d, name + ".ljs")
+    lo, hi = scene_box(blob)
+    rays = random_rays(100_000, lo, hi, seed=11)
+    results = {}
+    for tag, env in (("cooperative", {}), ("launches", {"LJ_PLOC_COOP": "0", "LJ_BVH8_COOP": "0"}), ("handover64", {"LJ_PLOC_STOP": "64"})):
+        for k in ("LJ_PLOC_COOP", "LJ_BVH8_COOP", "LJ_PLOC_STOP"):
+            monkeypatch.delenv(k, raising=False)
+        for k, v in env.items():
+            monkeypatch.setenv(k, v)
+        sc = gpu.load_scene(blob)
+        try:
+            results[tag] = (sc.build_stats.bvh_nodes, sc.intersect(rays), sc.intersect(rays, any_hit=True), sc.build_stats.bvh_build_ms)
+        finally:
+            sc.close()
+    n0, h0, o0, ms0 = results["cooperative"]
+    print(f"{name}: {n0} nodes; build ms " + ", ".join(f"{k} {v[3]:.2f}" for k, v in results.items()))
+    for tag in ("launches", "handover64"):
+        n, h, o, _ = results[tag]
+        assert n == n0, f"{tag}: {n} nodes against {n0}"
+        for f in ("geom_id", "prim_id", "t", "u", "v", "ng"):
+            assert np.array_equal(h0[f], h[f]), f"{tag}: closest-hit field {f} differs"
+        assert np.array_equal(o0["t"], o["t"])
