@@ -202,6 +202,10 @@ LJ_D bool bounce_at_vertex(const DScene &sc, Sink &out, int slot, const PathVert
 #ifndef LJ_SHADE_MIN_BLOCKS
 #define LJ_SHADE_MIN_BLOCKS 4
 #endif
+#ifndef LJ_SHADE_MIN_BLOCKS_LAMBERTIAN
+#define LJ_SHADE_MIN_BLOCKS_LAMBERTIAN LJ_SHADE_MIN_BLOCKS
+#endif
+constexpr int shade_min_blocks(int kind) { return kind == LJ_MAT_LAMBERTIAN ? LJ_SHADE_MIN_BLOCKS_LAMBERTIAN : LJ_SHADE_MIN_BLOCKS; }
 // One path vertex: finish the previous bounce with the new hit (emission + MIS, Russian roulette), then NEE + BSDF
 // sampling at the new vertex (path_tracing.h:58-61, :96-322).  Called by the lanes of a warp whose slot has a hit.
 template <int KIND, typename Sink>
@@ -277,7 +281,7 @@ LJ_D void shade_slot(const DScene &sc, const WfPool &wp, Sink &out, const int sl
 // slot records are then read and written fully coalesced (2 KB contiguous per warp) instead of gathered through the
 // queue, and the queue read drops out of the dependent-load chain.  Same per-slot arithmetic either way.
 template <int KIND, bool SLOTS>
-__global__ void __launch_bounds__(128, LJ_SHADE_MIN_BLOCKS) k_wf_shade(DScene sc, WfPool wp, int n_upper) {
+__global__ void __launch_bounds__(128, shade_min_blocks(KIND)) k_wf_shade(DScene sc, WfPool wp, int n_upper) {
     const int n = SLOTS ? wp.capacity : min(n_upper, wp.counts[Q_KIND0 + KIND]);
     const int *queue = wp.q_kind[KIND];
     const int lane = threadIdx.x & 31;
