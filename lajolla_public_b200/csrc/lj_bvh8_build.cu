@@ -275,6 +275,12 @@ int lj_bvh8_collapse(int n, const int *d_root2, const float4 *tri_verts, const i
     if (const char *e = getenv("LJ_OPEN_LEAVES")) a.open_leaves = atoi(e) != 0;
     bool coop = true;
     if (const char *e = getenv("LJ_BVH8_COOP")) coop = atoi(e) != 0;
+    if (coop) {                       // a device without cooperative launches gets one launch per level
+        int dev = 0, ok = 0;
+        CK(cudaGetDevice(&dev));
+        CK(cudaDeviceGetAttribute(&ok, cudaDevAttrCooperativeLaunch, dev));
+        coop = ok != 0;
+    }
     if (coop) {
         int per_sm = 0, dev = 0, sm_count = 0;
         CK(cudaGetDevice(&dev));

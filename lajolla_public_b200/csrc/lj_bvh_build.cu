@@ -682,6 +682,12 @@ static int ploc_build(int n, const int *vals, const float4 *prim_lo, const float
     const bool trace = getenv("LJ_BVH_TRACE") != nullptr;
     bool coop = use_tail;                       // LJ_PLOC_COOP=0: the launch sequence with a read-back every LJ_PLOC_BATCH rounds
     if (const char *e = getenv("LJ_PLOC_COOP")) coop = coop && atoi(e) != 0;
+    if (coop) {                                 // a device (or a partition of one) without cooperative launches gets the launch sequence
+        int dev = 0, ok = 0;
+        CK(cudaGetDevice(&dev));
+        CK(cudaDeviceGetAttribute(&ok, cudaDevAttrCooperativeLaunch, dev));
+        coop = ok != 0;
+    }
     int cur = 0;
     if (coop) {
         const int chunks = (n + PLOC_B - 1) / PLOC_B;
