@@ -19,6 +19,9 @@
 #ifndef LJ_BVH8_STACK
 #define LJ_BVH8_STACK 32
 #endif
+#ifndef LJ_STACK_TOP_CACHE
+#define LJ_STACK_TOP_CACHE 0
+#endif
 
 LJ_D unsigned byte_of(unsigned w, int i) { return (w >> (8 * i)) & 0xffu; }
 
@@ -36,6 +39,7 @@ struct Trav8 {
     uint2 ng;        // node group: x = child base, y = (pending inner-child hits << 24) | imask
     uint2 tg;        // primitive group waiting to be tested: x = first slot, y = 24-bit pending mask
     int sp;
+    uint2 top;                    // the stack's top entry lives in registers (LJ_STACK_TOP_CACHE): logical stack = stack[0 .. sp-2] + top
     uint2 stack[LJ_BVH8_STACK];   // node groups (y & 0xff000000 != 0) and postponed primitive groups (top byte 0)
     unsigned n_nodes, n_prims;
 
@@ -50,9 +54,23 @@ struct Trav8 {
         best_t = r.tfar; best_slot = -1;
         ng = make_uint2(0u, 0x80000000u);      // root: one pending inner child, empty imask
         tg = make_uint2(0u, 0u);
-        sp = 0; n_nodes = 0; n_prims = 0;
+        sp = 0; top = make_uint2(0u, 0u); n_nodes = 0; n_prims = 0;
     }
 
+    // LJ_STACK_TOP_CACHE=1 (experiment, OFF): push / pop with the top entry cached in `top` -- a pop hands out the register
+    // and starts the load of the entry below, which is not needed before the NEXT pop, so the local-memory latency leaves
+    // the refill's critical path (the refill loop is 19 % of the extend kernel's stall samples at 4-5 active lanes).  The
+    // two extra registers do not fit the 48 the trace kernels are compiled for: k_wf_extend's spills went from 84 to 404
+    // bytes and sponza's extend stage from 74.4 to 84.4 ms (profiles/r02_experiments.md).  Same entries, same order.
+#if LJ_STACK_TOP_CACHE
+    LJ_D void push(uint2 e) { if (sp > 0) stack[sp - 1] = top; top = e; sp++; }
+    LJ_D uint2 peek() const { return top; }
+    LJ_D void pop() { sp--; if (sp > 0) top = stack[sp - 1]; }
+#else
+    LJ_D void push(uint2 e) { stack[sp++] = e; }
+    LJ_D uint2 peek() const { return stack[sp - 1]; }
+    LJ_D void pop() { sp--; }
+#endif
     LJ_D bool wants_node() const { return (ng.y & 0xff000000u) != 0u; }
     LJ_D bool wants_prim() const { return tg.y != 0u; }
     LJ_D bool active() const { return wants_node() || wants_prim(); }
@@ -91,9 +109,9 @@ struct Trav8 {
     // on its primitive work (wants_node() false, wants_prim() true).
     LJ_D void refill_from_stack() {
         while (!wants_node() && sp > 0) {
-            const uint2 e = stack[sp - 1];
-            if (e.y & 0xff000000u) { ng = e; sp--; }
-            else if (tg.y == 0u) { tg = e; sp--; }
+            const uint2 e = peek();
+            if (e.y & 0xff000000u) { ng = e; pop(); }
+            else if (tg.y == 0u) { tg = e; pop(); }
             else break;
         }
     }
@@ -107,7 +125,7 @@ struct Trav8 {
     LJ_D bool node_step(const DScene &sc) {
         const int bit = 31 - __clz(ng.y);
         ng.y &= ~(1u << bit);
-        if ((ng.y & 0xff000000u) && sp < LJ_BVH8_STACK) stack[sp++] = ng;
+        if ((ng.y & 0xff000000u) && sp < LJ_BVH8_STACK) push(ng);
         const unsigned slot = (unsigned)(bit - 24) ^ oct_inv;
         const unsigned rel = __popc(ng.y & 0xffu & ((1u << slot) - 1u));
         const float4 *np = reinterpret_cast<const float4 *>(&sc.bvh8[ng.x + rel]);
@@ -165,7 +183,7 @@ struct Trav8 {
         const uint2 ntg = make_uint2(__float_as_uint(n1.y), hitmask & 0x00ffffffu);
         if (ntg.y) {
             if (tg.y == 0u) tg = ntg;
-            else if (sp < LJ_BVH8_STACK) stack[sp++] = ntg;
+            else if (sp < LJ_BVH8_STACK) push(ntg);
             else {                                  // stack full (never seen in practice): test the new group right away
                 unsigned m = ntg.y;
                 while (m) {

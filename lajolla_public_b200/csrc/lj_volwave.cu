@@ -135,7 +135,7 @@ __global__ void __launch_bounds__(128, 10) k_vol_extend(DScene sc, VolPool vp, i
     const int n = min(n_upper, vp.counts[VQ_EXT]);
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
-    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0; tv.top = make_uint2(0u, 0u);
     unsigned nn = 0, np = 0;
     while (true) {
         if (ray_idx >= 0 && !tv.active()) {

@@ -35,7 +35,7 @@ __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_extend(DScene s
     if (blockIdx.x == 0 && threadIdx.x == 0) wp.counts[Q_REGEN] = 0;    // drained by the generate stage (see k_wf_generate)
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
-    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0; tv.top = make_uint2(0u, 0u);
     unsigned nn = 0, np = 0;
     while (true) {
         // retire finished lanes together (the hit reconstruction runs with as many lanes as possible)
@@ -95,7 +95,7 @@ __global__ void __launch_bounds__(128, LJ_TRACE_MIN_BLOCKS) k_wf_shadow(DScene s
     const int n = min(n_upper, wp.counts[Q_SHADOW]);
     int ray_idx = -1; bool exhausted = false;
     Trav8 tv;
-    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0;
+    tv.ng = make_uint2(0u, 0u); tv.tg = make_uint2(0u, 0u); tv.sp = 0; tv.top = make_uint2(0u, 0u);
     bool found = false;
     unsigned nn = 0, np = 0;
     while (true) {

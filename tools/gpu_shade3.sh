@@ -1,7 +1,7 @@
 #!/bin/bash
 set -u
-timeout 600 python -m pytest tests/test_gpu_parity.py -m gpu -x -q 2>&1 | tail -1
-for s in "sponza 64" "cbox 64" "veach_mi 64" "sponza 8"; do for rep in 1 2; do
+timeout 600 python -m pytest tests/test_gpu_parity.py tests/test_gpu_raycast.py tests/test_gpu_seam.py -m gpu -x -q 2>&1 | tail -1
+for s in "sponza 64" "cbox 64"; do for rep in 1 2; do
   timeout 300 python tools/profile_stages.py $s 2>/dev/null | python -c "
 import json,sys
 d=json.load(sys.stdin); s=d['stage_ms']
