@@ -297,8 +297,6 @@ LJ_D double sp_max(d3 a) { return max3(a); }
 LJ_D double sp_max(double a) { return a; }
 LJ_D double sp_comp(d3 a, int c) { return comp(a, c); }
 LJ_D double sp_comp(double a, int) { return a; }
-LJ_D d3 sp_div(d3 a, double s) { return a / s; }
-LJ_D double sp_div(double a, double s) { double inv = 1.0 / s; return a * inv; }      // one channel of `d3 / double` (vector.h:193-197)
 LJ_D d3 sp_quot(d3 a, d3 b) { return a / b; }                                        // d3 / d3: true division per channel
 LJ_D double sp_quot(double a, double b) { return div_z(a, b); }
 
@@ -325,7 +323,9 @@ LJ_D void medium_sigma_sa(const DScene &sc, const lj_medium &m, d3 p, double &si
     sigma_a = density * (1.0 - albedo);
 }
 
-template <typename S> struct TrackStateT { S majorant; double maj_c, accum_t; int channel, iteration; bool active; };
+// inv_mx = 1 / max(majorant): the reciprocal every `spectrum / max(majorant)` of a step multiplies by (vector.h:193-197), computed once
+// per segment instead of once per step -- same operands, same value
+template <typename S> struct TrackStateT { S majorant; double maj_c, accum_t, inv_mx; int channel, iteration; bool active; };
 typedef TrackStateT<d3> TrackState;
 
 template <typename S>
@@ -336,8 +336,12 @@ LJ_D void track_begin(const DScene &sc, const lj_medium &media, const Ray &ray, 
     ts.accum_t = 0;
     ts.iteration = 0;
     ts.maj_c = sp_comp(ts.majorant, ts.channel);
+    ts.inv_mx = 1.0 / sp_max(ts.majorant);
     ts.active = !(ts.maj_c <= 0) && !(ts.iteration >= sc.options.max_null_collisions);
 }
+// `a / s` of a spectrum by a scalar whose reciprocal is at hand: the multiplications of operator/(d3, double)
+LJ_D d3 sp_mul_inv(d3 a, double inv) { return mk3(a.x * inv, a.y * inv, a.z * inv); }
+LJ_D double sp_mul_inv(double a, double inv) { return a * inv; }
 
 // One iteration of the NEE ratio-tracking loop (vol_path_tracing.h:364-408).
 template <typename S>
@@ -355,10 +359,10 @@ LJ_D void ratio_track_step(const DScene &sc, const lj_medium &media, d3 p, d3 di
         S real_prob = sp_quot(sigma_t, majorant);       // sigma_t / majorant; zero in empty voxels: div_z
         S sigma_n = majorant * (1.0 - real_prob);
         S e = sp_exp(-majorant * t);
-        double mx = sp_max(majorant);
-        transmittance_light = transmittance_light * sp_div(e * sigma_n, mx);
-        p_trans_nee = p_trans_nee * sp_div(e * majorant, mx);
-        p_trans_dir = p_trans_dir * sp_div(e * majorant * (1.0 - real_prob), mx);
+        const double inv_mx = ts.inv_mx;               // `x / max(majorant)` = x * (1 / max(majorant)), vector.h:193-197
+        transmittance_light = transmittance_light * sp_mul_inv(e * sigma_n, inv_mx);
+        p_trans_nee = p_trans_nee * sp_mul_inv(e * majorant, inv_mx);
+        p_trans_dir = p_trans_dir * sp_mul_inv(e * majorant * (1.0 - real_prob), inv_mx);
         if (sp_max(transmittance_light) <= 0) { ts.active = false; return; }
     } else {
         S e = sp_exp(-majorant * dt);
@@ -396,17 +400,17 @@ LJ_D void free_flight_step(const DScene &sc, const lj_medium &media, Ray &ray, d
         S real_prob = sp_quot(sigma_t, majorant);       // sigma_t / majorant; zero in empty voxels: div_z
         S sigma_n = majorant * (1.0 - real_prob);
         S e = sp_exp(-majorant * t);
-        double mx = sp_max(majorant);
+        const double inv_mx = ts.inv_mx;               // `x / max(majorant)` = x * (1 / max(majorant)), vector.h:193-197
         if (pcg_real(rng) < sp_comp(real_prob, ts.channel)) {
-            transmittance = transmittance * sp_div(e, mx);
-            trans_dir_pdf = trans_dir_pdf * sp_div(e * majorant * real_prob, mx);
+            transmittance = transmittance * sp_mul_inv(e, inv_mx);
+            trans_dir_pdf = trans_dir_pdf * sp_mul_inv(e * majorant * real_prob, inv_mx);
             ray.org = p;
             scatter = true;
             ts.active = false; return;
         } else {
-            transmittance = transmittance * sp_div(e * sigma_n, mx);
-            trans_dir_pdf = trans_dir_pdf * sp_div(e * majorant * (1.0 - real_prob), mx);
-            trans_nee_pdf = trans_nee_pdf * sp_div(e * majorant, mx);
+            transmittance = transmittance * sp_mul_inv(e * sigma_n, inv_mx);
+            trans_dir_pdf = trans_dir_pdf * sp_mul_inv(e * majorant * (1.0 - real_prob), inv_mx);
+            trans_nee_pdf = trans_nee_pdf * sp_mul_inv(e * majorant, inv_mx);
         }
     } else {
         S e = sp_exp(-majorant * dt);

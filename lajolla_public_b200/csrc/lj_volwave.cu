@@ -306,7 +306,7 @@ __global__ void __launch_bounds__(128, GREY ? LJ_VOL_TRACK_GREY_MIN_BLOCKS : LJ_
                 const VolTrack tr = vp.track[slot];
                 if (!NEE) { narrow3(mk3(tr.tx, tr.ty, tr.tz), A); narrow3(mk3(tr.dx, tr.dy, tr.dz), Bv); narrow3(mk3(tr.nx, tr.ny, tr.nz), Cv); }
                 narrow3(mk3(tr.mjx, tr.mjy, tr.mjz), ts.majorant); ts.accum_t = tr.accum_t; ts.channel = tr.channel; ts.iteration = tr.iteration;
-                ts.maj_c = sp_comp(ts.majorant, ts.channel); ts.active = true;
+                ts.maj_c = sp_comp(ts.majorant, ts.channel); ts.inv_mx = 1.0 / sp_max(ts.majorant); ts.active = true;
             } else if (medium != -1) track_begin(sc, sc.media[medium], ray, rng, ts);
         }
         if (!__ballot_sync(0xffffffffu, item >= 0)) break;
